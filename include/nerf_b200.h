@@ -1,0 +1,184 @@
+/*
+ * nerf_b200.h -- C-ABI of the B200-native classic-NeRF hot path.
+ *
+ * This is the drop-in boundary.  The reference has no native boundary of
+ * its own except the un-vendored `torchsearchsorted` extension; every entry point below therefore
+ * cites the *Python* reference function whose arithmetic it replaces (paths relative to the
+ * reference checkout: "TF" = nerf/..., "PT" = nerf-pytorch/nerf/...).
+ *
+ * Conventions
+ *   - plain C types only: raw DEVICE pointers (unless a parameter is documented as HOST), sizes,
+ *     scalars, an opaque model handle and a cudaStream_t passed as void*;
+ *   - the caller owns all device memory.  Inputs are borrowed for the duration of the call,
+ *     outputs and workspaces are pre-allocated by the caller.  The library owns only the packed
+ *     weight copies behind an nb_model_t;
+ *   - every call is asynchronous on the given stream and never synchronises the device;
+ *   - return value 0 on success, negative nb_status on failure; nb_last_error() returns a
+ *     thread-local message.  Nothing throws across the ABI;
+ *   - all tensors are fp32, row-major, ray-major (ray = row*W + col) unless stated otherwise.
+ *   - there is no CPU fallback: without a CUDA device every compute call fails with NB_ERR_CUDA.
+ */
+#ifndef NERF_B200_H_
+#define NERF_B200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define NB_ABI_VERSION 1
+
+typedef enum nb_status {
+  NB_OK = 0,
+  NB_ERR_INVALID = -1,      /* bad argument */
+  NB_ERR_CUDA = -2,         /* CUDA runtime error (message holds cudaGetErrorString) */
+  NB_ERR_UNSUPPORTED = -3,  /* shape / option not supported by this kernel family */
+  NB_ERR_WORKSPACE = -4     /* workspace too small */
+} nb_status;
+
+/* MLP layer graphs. */
+typedef enum nb_graph {
+  NB_GRAPH_NERF = 0,     /* TF init_nerf_model: nerf/run_nerf_helpers.py:80-118 (D x W, skip after layer 4) */
+  NB_GRAPH_FLEXIBLE = 1  /* PT FlexibleNeRFModel at its 4x128 defaults: nerf-pytorch/nerf/models.py:185-256 */
+} nb_graph;
+
+typedef enum nb_precision {
+  NB_PREC_FP32 = 0, /* FFMA path: fp32 operands and accumulation, layer by layer */
+  NB_PREC_BF16 = 1  /* fused tcgen05 path: bf16 operands, fp32 accumulation in TMEM */
+} nb_precision;
+
+typedef struct nb_model nb_model_t;
+typedef void* nb_stream_t; /* cudaStream_t */
+
+/* ---------------------------------------------------------------- misc */
+int nb_abi_version(void);
+const char* nb_last_error(void);
+/* Number of CUDA devices visible, or a negative nb_status.  Never touches the oracle or a CPU path. */
+int nb_device_count(void);
+/* Kernels launched by this library on the calling thread since the last reset (bench.py: gpu_launches). */
+int64_t nb_launch_count(void);
+void nb_launch_count_reset(void);
+
+/* ---------------------------------------------------------------- model handle
+ * Replaces: TF create_nerf/init_nerf_model (nerf/run_nerf.py:378-404, run_nerf_helpers.py:80-118) and
+ * PT FlexibleNeRFModel.__init__ (models.py:186-231) as far as the *weights layout* is concerned.
+ * Parameters live in ONE caller-owned flat fp32 buffer: for every layer, in the canonical order
+ * reported by nb_model_tensor_info, weight [out, in] row-major (nn.Linear convention) followed by
+ * bias [out].  Names equal the reference state_dict keys for FLEXIBLE and
+ * pts_linears.i / alpha_linear / bottleneck_linear / views_linears.0 / rgb_linear / output_linear
+ * for NERF (Keras layer order of get_weights(), run_nerf.py:835-843).
+ */
+int nb_model_create(int graph, int depth, int width, int n_freq_xyz, int n_freq_dir, int use_viewdirs,
+                    int skip_layer /* NERF: index of the layer after which [pts,h] is concatenated, -1 = none */,
+                    nb_model_t** out);
+int nb_model_destroy(nb_model_t* m);
+int64_t nb_model_param_count(const nb_model_t* m);
+int nb_model_num_tensors(const nb_model_t* m);
+/* name_cap bytes are written to `name` (NUL terminated).  cols == 0 marks a bias vector of `rows`. */
+int nb_model_tensor_info(const nb_model_t* m, int index, char* name, int name_cap, int64_t* rows, int64_t* cols,
+                         int64_t* offset_floats);
+/* Borrow the flat parameter buffer (device).  Must stay valid until replaced or the model is destroyed. */
+int nb_model_set_params(nb_model_t* m, const float* flat_params, int64_t n_floats);
+/* (Re)build the kernel-side copies of the weights for `precision` from the flat buffer. */
+int nb_model_pack(nb_model_t* m, int precision, nb_stream_t stream);
+/* FLOPs (2*MAC, unpadded) of one forward evaluation of one point: SURVEY 8d "algorithmic flops". */
+int64_t nb_model_flops_per_point(const nb_model_t* m);
+
+/* ---------------------------------------------------------------- a1 ray generation
+ * Replaces get_rays (TF run_nerf_helpers.py:123-130) / get_ray_bundle (PT nerf_helpers.py:67-110).
+ * dir_cam = [(col-cx)/fx, -(row-cy)/fy, -1]; rays_d = sum_j dir_cam[j]*c2w[k][j]; rays_o = c2w[:,3].
+ * c2w34 is a HOST pointer to 12 floats (3x4 row-major).  Writes rows [row0,row1) of the image into
+ * rays_o / rays_d, each [(row1-row0)*W, 3].
+ */
+int nb_get_rays(int H, int W, float fx, float fy, float cx, float cy, const float* c2w34_host, int row0, int row1,
+                float* rays_o, float* rays_d, nb_stream_t stream);
+
+/* a3: ndc_rays (TF run_nerf_helpers.py:143-178 == PT nerf_helpers.py:170-197). In-place allowed.
+ * focal / near are doubles because the reference evaluates -1/(W/(2*focal)) with Python (double) scalars
+ * before the single rounding to fp32. */
+int nb_ndc_rays(int H, int W, double focal, double near, const float* rays_o, const float* rays_d, int64_t n,
+                float* ndc_o, float* ndc_d, nb_stream_t stream);
+
+/* a2+a3+a4: unit view directions from the PRE-NDC directions, optional NDC, pack [o,d,near,far,(viewdir)]
+ * (TF render run_nerf.py:297-325 == PT run_one_iter_of_nerf train_utils.py:141-168).
+ * viewdir_src may be NULL (then rays_d is used) -- it differs only for c2w_staticcam.
+ * near_arr/far_arr (device, [n]) override the scalars when non-NULL.  rays_out is [n, 8] or [n, 11]. */
+int nb_make_ray_batch(const float* rays_o, const float* rays_d, const float* viewdir_src, int64_t n, int use_viewdirs,
+                      int ndc, int H, int W, double focal, double near, double far, const float* near_arr,
+                      const float* far_arr, float* rays_out, nb_stream_t stream);
+
+/* ---------------------------------------------------------------- a5 stratified depths
+ * TF render_rays run_nerf.py:181-199 == PT predict_and_render_radiance train_utils.py:45-65.
+ * t_rand ([n,S] uniforms in [0,1)) may be NULL (perturb off). z_vals is [n,S]. */
+int nb_sample_coarse(const float* rays, int ray_stride, int64_t n, int n_samples, int lindisp, const float* t_rand,
+                     float* z_vals, nb_stream_t stream);
+
+/* ---------------------------------------------------------------- a6 positional encoding
+ * Embedder.embed (TF run_nerf_helpers.py:22-56) == positional_encoding (PT nerf_helpers.py:113-157).
+ * x [n, 3] -> out [n, out_stride] (first 3+6L columns written; [x, sin(2^0 x), cos(2^0 x), ...]). */
+int nb_posenc(const float* x, int64_t n, int n_freqs, int include_input, float* out, int out_stride,
+              nb_stream_t stream);
+
+/* ---------------------------------------------------------------- a7/a8 MLP
+ * Replaces run_network + the network forward (TF run_nerf.py:30-45 + run_nerf_helpers.py:80-118;
+ * PT train_utils.py:8-25 + models.py:233-256).  Points are o + d*z (rays/z form) or explicit.
+ * raw is [n_rays*n_samples, 4] = [rgb, sigma] pre-activation.
+ * With save_for_backward the workspace keeps what nb_mlp_backward needs (same workspace must be passed). */
+size_t nb_mlp_workspace_bytes(const nb_model_t* m, int precision, int64_t n_points, int save_for_backward);
+int nb_mlp_forward(const nb_model_t* m, int precision, const float* rays, int ray_stride, const float* z_vals,
+                   int64_t n_rays, int n_samples, float* raw, void* workspace, size_t workspace_bytes,
+                   int save_for_backward, nb_stream_t stream);
+/* Explicit points [n_points,3]; viewdirs [n_points/points_per_dir, 3] or NULL (network_query_fn form). */
+int nb_mlp_forward_points(const nb_model_t* m, int precision, const float* pts, const float* viewdirs,
+                          int64_t n_points, int points_per_dir, float* raw, void* workspace, size_t workspace_bytes,
+                          nb_stream_t stream);
+/* Autograd of the network w.r.t. its parameters (TF train():807-826, PT train_nerf.py:286).
+ * d_raw [n_points,4] is consumed (overwritten).  flat_grad (same layout as the flat parameters) is
+ * ACCUMULATED into.  No gradient is produced for points / rays (nothing trainable upstream). */
+int nb_mlp_backward(const nb_model_t* m, int precision, int64_t n_points, float* d_raw, void* workspace,
+                    size_t workspace_bytes, float* flat_grad, nb_stream_t stream);
+
+/* ---------------------------------------------------------------- a9 compositing
+ * raw2outputs (TF run_nerf.py:93-163) == volume_render_radiance_field (PT volume_rendering_utils.py:6-53).
+ * noise ([n,S], already multiplied by raw_noise_std) may be NULL.  depth / weights may be NULL. */
+int nb_composite(const float* raw, const float* z_vals, const float* rays, int ray_stride, int64_t n, int n_samples,
+                 const float* noise, int white_bkgd, float* rgb, float* disp, float* acc, float* depth,
+                 float* weights, nb_stream_t stream);
+/* Backward of the above w.r.t. raw.  Any of d_rgb [n,3], d_disp, d_acc, d_depth [n] may be NULL (= zero). */
+int nb_composite_backward(const float* raw, const float* z_vals, const float* rays, int ray_stride, int64_t n,
+                          int n_samples, const float* noise, int white_bkgd, const float* d_rgb,
+                          const float* d_disp, const float* d_acc, const float* d_depth, float* d_raw,
+                          nb_stream_t stream);
+
+/* ---------------------------------------------------------------- a10/a11 hierarchical sampling
+ * The reference's only native boundary: torchsearchsorted.searchsorted(a[B,n], v[B,m], side) -> int64[B,m]
+ * (PT nerf_helpers.py:241-243,286-288; un-vendored github.com/aliutkus/torchsearchsorted, unpinned).
+ * side_right != 0 counts entries <= v (numpy side='right').  a_rows == 1 broadcasts a over the rows of v. */
+int nb_searchsorted(const float* a, int64_t a_rows, int n, const float* v, int64_t v_rows, int m, int side_right,
+                    int64_t* out, nb_stream_t stream);
+/* sample_pdf (TF run_nerf_helpers.py:183-211) == sample_pdf_2 (PT nerf_helpers.py:260-302).
+ * bins [n, nb], weights [n, nb-1] with row strides; u ([n, ns]) NULL => deterministic linspace(0,1,ns).
+ * samples [n, ns].  cdf_out ([n, nb], optional) receives the fp32 CDF actually used. */
+int nb_sample_pdf(const float* bins, int bins_stride, const float* weights, int weights_stride, int64_t n, int nb,
+                  const float* u, int ns, float* samples, float* cdf_out, nb_stream_t stream);
+/* The fused form used by the renderer: from the coarse z_vals [n,S] and coarse weights [n,S] produce
+ * z_samples [n,ns] (may be NULL) and the merged, sorted z_fine [n,S+ns]
+ * (TF run_nerf.py:213-221 == PT train_utils.py:93-105: mids, weights[1:-1], sample_pdf, sort(cat)).
+ * z_std ([n], optional) = population std of z_samples (TF run_nerf.py:238). */
+int nb_sample_fine(const float* z_vals, const float* weights, int64_t n, int n_samples, const float* u, int ns,
+                   float* z_samples, float* z_fine, float* z_std, nb_stream_t stream);
+/* Ascending merge of two row-wise sorted arrays (torch.sort(cat) / tf.sort(concat), values only). */
+int nb_merge_sorted(const float* a, int na, const float* b, int nb, int64_t n, float* out, nb_stream_t stream);
+
+/* ---------------------------------------------------------------- a13 loss
+ * img2mse (TF run_nerf_helpers.py:11, PT nerf_helpers.py:9): loss_out[0] += mean((pred-target)^2) and
+ * d_pred = grad_scale * 2*(pred-target)/count.  loss_out must be zeroed by the caller. */
+int nb_mse_loss(const float* pred, const float* target, int64_t count, float grad_scale, float* loss_out,
+                float* d_pred, nb_stream_t stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* NERF_B200_H_ */
