@@ -57,7 +57,7 @@ int nb_abi_version(void);
 const char* nb_last_error(void);
 /* Number of CUDA devices visible, or a negative nb_status.  Never touches the oracle or a CPU path. */
 int nb_device_count(void);
-/* Kernels launched by this library on the calling thread since the last reset (bench.py: gpu_launches). */
+/* Kernels launched by this library (all threads of the process) since the last reset (bench.py: gpu_launches). */
 int64_t nb_launch_count(void);
 void nb_launch_count_reset(void);
 
@@ -171,6 +171,62 @@ int nb_sample_fine(const float* z_vals, const float* weights, int64_t n, int n_s
                    float* z_samples, float* z_fine, float* z_std, nb_stream_t stream);
 /* Ascending merge of two row-wise sorted arrays (torch.sort(cat) / tf.sort(concat), values only). */
 int nb_merge_sorted(const float* a, int na, const float* b, int nb, int64_t n, float* out, nb_stream_t stream);
+
+/* ---------------------------------------------------------------- a5..a12 per-chunk renderer
+ * The whole of render_rays (TF nerf/run_nerf.py:48-243) == predict_and_render_radiance
+ * (PT nerf-pytorch/nerf/train_utils.py:28-127) for one chunk of packed rays, as ONE call:
+ * stratified depths -> coarse MLP -> compositing -> sample_pdf + sorted merge -> fine MLP -> compositing.
+ * This is the entry point the reference-facing Python API (render / run_one_iter_of_nerf) sits on. */
+typedef struct nb_render_cfg {
+  int n_samples;         /* N_samples / num_coarse */
+  int n_importance;      /* N_importance / num_fine; 0 = coarse pass only */
+  int lindisp;
+  int white_bkgd;
+  int precision;         /* nb_precision of both MLP passes */
+  int save_for_backward; /* keep what nb_render_rays_backward needs in the workspace */
+} nb_render_cfg;
+
+/* Random inputs (device, all optional): the reference draws them from the framework RNG, so parity is
+ * defined only when they are NULL (perturb = 0, raw_noise_std = 0) or supplied by the test. */
+typedef struct nb_render_rand {
+  const float* t_rand;  /* [n, n_samples] uniforms for the stratified jitter (run_nerf.py:192-199) */
+  const float* u_fine;  /* [n, n_importance] uniforms for sample_pdf (run_nerf_helpers.py:192-197) */
+  const float* noise_c; /* [n, n_samples] sigma noise, already scaled by raw_noise_std (run_nerf.py:130-132) */
+  const float* noise_f; /* [n, n_samples + n_importance] */
+} nb_render_rand;
+
+/* Outputs (device, any may be NULL).  With n_importance == 0 the coarse result is written to
+ * rgb/disp/acc/depth and the *0 pointers are ignored. */
+typedef struct nb_render_out {
+  float *rgb, *disp, *acc, *depth;     /* [n,3] [n] [n] [n]   fine pass  (rgb_map, disp_map, acc_map, depth_map) */
+  float *rgb0, *disp0, *acc0, *depth0; /* coarse pass (extras rgb0 / disp0 / acc0) */
+  float* z_std;                        /* [n] std of the importance samples (run_nerf.py:238) */
+  float* raw;                          /* [n, S(+I), 4] last-pass raw network output (retraw) */
+  float* z_vals;                       /* [n, S(+I)] last-pass depths */
+  float* weights;                      /* [n, S(+I)] last-pass compositing weights */
+} nb_render_out;
+
+/* Upstream gradients for nb_render_rays_backward (device, any may be NULL = zero). */
+typedef struct nb_render_grads {
+  const float *d_rgb, *d_disp, *d_acc, *d_depth;
+  const float *d_rgb0, *d_disp0, *d_acc0, *d_depth0;
+} nb_render_grads;
+
+size_t nb_render_workspace_bytes(const nb_model_t* coarse, const nb_model_t* fine, int ray_stride, int64_t n,
+                                 const nb_render_cfg* cfg);
+/* `fine` may be NULL (the coarse network is then reused for the importance pass, run_nerf.py:226). */
+int nb_render_rays(const nb_model_t* coarse, const nb_model_t* fine, const float* rays, int ray_stride, int64_t n,
+                   const nb_render_cfg* cfg, const nb_render_rand* rnd, const nb_render_out* out, void* workspace,
+                   size_t workspace_bytes, nb_stream_t stream);
+/* Autograd of the call above w.r.t. the network parameters (TF train():807-826 / PT train_nerf.py:286):
+ * compositing backward and MLP backward for the fine and the coarse pass; no gradient flows through
+ * sample_pdf (stop_gradient, run_nerf.py:218 / detach, train_utils.py:103).  Same rays / cfg / rnd / workspace
+ * as the forward call made with save_for_backward.  grad_coarse / grad_fine are flat buffers in the
+ * parameter layout and are ACCUMULATED into (grad_fine may alias grad_coarse when fine == NULL). */
+int nb_render_rays_backward(const nb_model_t* coarse, const nb_model_t* fine, const float* rays, int ray_stride,
+                            int64_t n, const nb_render_cfg* cfg, const nb_render_rand* rnd,
+                            const nb_render_grads* grads, void* workspace, size_t workspace_bytes,
+                            float* grad_coarse, float* grad_fine, nb_stream_t stream);
 
 /* ---------------------------------------------------------------- a13 loss
  * img2mse (TF run_nerf_helpers.py:11, PT nerf_helpers.py:9): loss_out[0] += mean((pred-target)^2) and

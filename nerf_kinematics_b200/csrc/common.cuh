@@ -1,6 +1,8 @@
 // Shared host/device helpers for the sm_100a kernels behind include/nerf_b200.h.
 #pragma once
 #include <cuda_runtime.h>
+
+#include <atomic>
 #include <stdint.h>
 #include <stdio.h>
 #include <string.h>
@@ -11,7 +13,7 @@ namespace nb {
 
 // ---- error plumbing (thread-local message, never throws across the ABI)
 void set_error(const char* fmt, ...);
-extern thread_local int64_t g_launches;
+extern std::atomic<int64_t> g_launches;  // process-wide: autograd runs backward on its own thread
 
 #define NB_REQUIRE(cond, ...)                \
   do {                                       \

@@ -1,0 +1,174 @@
+// Per-chunk renderer: the body of render_rays (nerf/run_nerf.py:48-243) == predict_and_render_radiance
+// (nerf-pytorch/nerf/train_utils.py:28-127) as one C-ABI call, and its backward for the train step.
+// It sequences the stage kernels of stages.cu / volume.cu and the MLP passes on the caller's stream;
+// all intermediates (depths, raw network output, weights) live in the caller-provided workspace.
+#include <algorithm>
+
+#include "model.h"
+
+namespace nb {
+
+struct RenderLayout {
+  size_t off_zc = 0, off_rawc = 0, off_wc = 0, off_zf = 0, off_rawf = 0, off_scratch = 0, off_draw = 0, off_mlp_c = 0,
+         off_mlp_f = 0, mlp_c_bytes = 0, mlp_f_bytes = 0, total = 0;
+};
+
+static RenderLayout render_layout(const nb_model* coarse, const nb_model* fine, int64_t n, const nb_render_cfg& c) {
+  RenderLayout L;
+  const int S = c.n_samples, I = c.n_importance;
+  const int64_t nn = n > 0 ? n : 1;
+  size_t off = 0;
+  auto take = [&](size_t bytes) {
+    size_t o = off;
+    off += (size_t)round_up((int64_t)bytes, 256);
+    return o;
+  };
+  L.off_zc = take(sizeof(float) * nn * S);
+  L.off_rawc = take(sizeof(float) * nn * S * 4);
+  L.off_wc = take(sizeof(float) * nn * S);
+  L.off_scratch = take(sizeof(float) * nn * 3);
+  if (I > 0) {
+    L.off_zf = take(sizeof(float) * nn * (S + I));
+    L.off_rawf = take(sizeof(float) * nn * (S + I) * 4);
+  }
+  const nb_model* mf = fine ? fine : coarse;
+  L.mlp_c_bytes = nb_mlp_workspace_bytes(coarse, c.precision, nn * S, c.save_for_backward);
+  L.mlp_f_bytes = I > 0 ? nb_mlp_workspace_bytes(mf, c.precision, nn * (S + I), c.save_for_backward) : 0;
+  if (c.save_for_backward) {
+    L.off_draw = take(sizeof(float) * nn * (S + I) * 4);
+    L.off_mlp_c = take(L.mlp_c_bytes);
+    L.off_mlp_f = take(L.mlp_f_bytes);
+  } else {
+    L.off_mlp_c = L.off_mlp_f = take(std::max(L.mlp_c_bytes, L.mlp_f_bytes));
+  }
+  L.total = off;
+  return L;
+}
+
+static inline float* at(void* ws, size_t off) { return reinterpret_cast<float*>(static_cast<char*>(ws) + off); }
+
+}  // namespace nb
+
+using namespace nb;
+
+#define NB_TRY(x)          \
+  do {                     \
+    int rc_ = (x);         \
+    if (rc_ != NB_OK) return rc_; \
+  } while (0)
+
+static int check_cfg(const nb_model_t* coarse, int ray_stride, int64_t n, const nb_render_cfg* cfg) {
+  NB_REQUIRE(coarse != nullptr && cfg != nullptr, "nb_render_rays: null model or cfg");
+  NB_REQUIRE(n >= 0 && cfg->n_samples >= 2 && cfg->n_importance >= 0, "nb_render_rays: bad sizes");
+  NB_REQUIRE(cfg->n_importance == 0 || cfg->n_samples >= 4, "nb_render_rays: hierarchical sampling needs N_samples >= 4");
+  NB_REQUIRE(ray_stride == 8 || ray_stride == 11, "nb_render_rays: ray_stride must be 8 or 11");
+  return NB_OK;
+}
+
+extern "C" {
+
+size_t nb_render_workspace_bytes(const nb_model_t* coarse, const nb_model_t* fine, int ray_stride, int64_t n,
+                                 const nb_render_cfg* cfg) {
+  if (check_cfg(coarse, ray_stride, n, cfg) != NB_OK) return 0;
+  return render_layout(coarse, fine, n, *cfg).total;
+}
+
+int nb_render_rays(const nb_model_t* coarse, const nb_model_t* fine, const float* rays, int ray_stride, int64_t n,
+                   const nb_render_cfg* cfg, const nb_render_rand* rnd, const nb_render_out* out, void* ws,
+                   size_t ws_bytes, nb_stream_t stream) {
+  NB_TRY(check_cfg(coarse, ray_stride, n, cfg));
+  NB_REQUIRE(out != nullptr, "nb_render_rays: null out");
+  if (n == 0) return NB_OK;
+  NB_REQUIRE(rays != nullptr, "nb_render_rays: null rays");
+  const RenderLayout L = render_layout(coarse, fine, n, *cfg);
+  if (ws == nullptr || ws_bytes < L.total) {
+    set_error("nb_render_rays: workspace of %zu bytes given, %zu needed", ws_bytes, L.total);
+    return NB_ERR_WORKSPACE;
+  }
+  const nb_render_rand none{nullptr, nullptr, nullptr, nullptr};
+  const nb_render_rand& r = rnd ? *rnd : none;
+  const int S = cfg->n_samples, I = cfg->n_importance;
+  const bool hier = I > 0;
+  float* zc = at(ws, L.off_zc);
+  float* rawc = at(ws, L.off_rawc);
+  float* wc = at(ws, L.off_wc);
+  float* scratch = at(ws, L.off_scratch);
+  void* mlp_c = static_cast<char*>(ws) + L.off_mlp_c;
+  void* mlp_f = static_cast<char*>(ws) + L.off_mlp_f;
+
+  NB_TRY(nb_sample_coarse(rays, ray_stride, n, S, cfg->lindisp, r.t_rand, zc, stream));
+  NB_TRY(nb_mlp_forward(coarse, cfg->precision, rays, ray_stride, zc, n, S, rawc, mlp_c, L.mlp_c_bytes,
+                        cfg->save_for_backward, stream));
+  // coarse compositing; its weights feed sample_pdf
+  float* c_rgb = hier ? (out->rgb0 ? out->rgb0 : scratch) : (out->rgb ? out->rgb : scratch);
+  NB_TRY(nb_composite(rawc, zc, rays, ray_stride, n, S, r.noise_c, cfg->white_bkgd, c_rgb, hier ? out->disp0 : out->disp,
+                      hier ? out->acc0 : out->acc, hier ? out->depth0 : out->depth, wc, stream));
+  const float* last_raw = rawc;
+  const float* last_z = zc;
+  const float* last_w = wc;
+  int last_S = S;
+  if (hier) {
+    float* zf = at(ws, L.off_zf);
+    float* rawf = at(ws, L.off_rawf);
+    NB_TRY(nb_sample_fine(zc, wc, n, S, r.u_fine, I, nullptr, zf, out->z_std, stream));
+    const nb_model_t* mf = fine ? fine : coarse;
+    NB_TRY(nb_mlp_forward(mf, cfg->precision, rays, ray_stride, zf, n, S + I, rawf, mlp_f, L.mlp_f_bytes,
+                          cfg->save_for_backward, stream));
+    NB_TRY(nb_composite(rawf, zf, rays, ray_stride, n, S + I, r.noise_f, cfg->white_bkgd, out->rgb ? out->rgb : scratch,
+                        out->disp, out->acc, out->depth, out->weights, stream));
+    last_raw = rawf;
+    last_z = zf;
+    last_w = nullptr;  // written directly above
+    last_S = S + I;
+  }
+  const cudaStream_t s = as_stream(stream);
+  if (out->raw) NB_CUDA(cudaMemcpyAsync(out->raw, last_raw, sizeof(float) * n * last_S * 4, cudaMemcpyDeviceToDevice, s));
+  if (out->z_vals) NB_CUDA(cudaMemcpyAsync(out->z_vals, last_z, sizeof(float) * n * last_S, cudaMemcpyDeviceToDevice, s));
+  if (out->weights && last_w)
+    NB_CUDA(cudaMemcpyAsync(out->weights, last_w, sizeof(float) * n * last_S, cudaMemcpyDeviceToDevice, s));
+  return NB_OK;
+}
+
+int nb_render_rays_backward(const nb_model_t* coarse, const nb_model_t* fine, const float* rays, int ray_stride,
+                            int64_t n, const nb_render_cfg* cfg, const nb_render_rand* rnd,
+                            const nb_render_grads* g, void* ws, size_t ws_bytes, float* grad_coarse,
+                            float* grad_fine, nb_stream_t stream) {
+  NB_TRY(check_cfg(coarse, ray_stride, n, cfg));
+  NB_REQUIRE(cfg->save_for_backward, "nb_render_rays_backward: the forward call was not made with save_for_backward");
+  NB_REQUIRE(g != nullptr && grad_coarse != nullptr, "nb_render_rays_backward: null grads");
+  if (n == 0) return NB_OK;
+  const RenderLayout L = render_layout(coarse, fine, n, *cfg);
+  if (ws == nullptr || ws_bytes < L.total) {
+    set_error("nb_render_rays_backward: workspace of %zu bytes given, %zu needed", ws_bytes, L.total);
+    return NB_ERR_WORKSPACE;
+  }
+  const nb_render_rand none{nullptr, nullptr, nullptr, nullptr};
+  const nb_render_rand& r = rnd ? *rnd : none;
+  const int S = cfg->n_samples, I = cfg->n_importance;
+  const bool hier = I > 0;
+  float* draw = at(ws, L.off_draw);
+  void* mlp_c = static_cast<char*>(ws) + L.off_mlp_c;
+  void* mlp_f = static_cast<char*>(ws) + L.off_mlp_f;
+  if (hier) {
+    const nb_model_t* mf = fine ? fine : coarse;
+    float* gf = fine ? grad_fine : grad_coarse;
+    NB_REQUIRE(gf != nullptr, "nb_render_rays_backward: null grad_fine");
+    if (g->d_rgb || g->d_disp || g->d_acc || g->d_depth) {
+      NB_TRY(nb_composite_backward(at(ws, L.off_rawf), at(ws, L.off_zf), rays, ray_stride, n, S + I, r.noise_f,
+                                   cfg->white_bkgd, g->d_rgb, g->d_disp, g->d_acc, g->d_depth, draw, stream));
+      NB_TRY(nb_mlp_backward(mf, cfg->precision, n * (S + I), draw, mlp_f, L.mlp_f_bytes, gf, stream));
+    }
+    if (g->d_rgb0 || g->d_disp0 || g->d_acc0 || g->d_depth0) {
+      NB_TRY(nb_composite_backward(at(ws, L.off_rawc), at(ws, L.off_zc), rays, ray_stride, n, S, r.noise_c,
+                                   cfg->white_bkgd, g->d_rgb0, g->d_disp0, g->d_acc0, g->d_depth0, draw, stream));
+      NB_TRY(nb_mlp_backward(coarse, cfg->precision, n * S, draw, mlp_c, L.mlp_c_bytes, grad_coarse, stream));
+    }
+  } else if (g->d_rgb || g->d_disp || g->d_acc || g->d_depth) {
+    NB_TRY(nb_composite_backward(at(ws, L.off_rawc), at(ws, L.off_zc), rays, ray_stride, n, S, r.noise_c,
+                                 cfg->white_bkgd, g->d_rgb, g->d_disp, g->d_acc, g->d_depth, draw, stream));
+    NB_TRY(nb_mlp_backward(coarse, cfg->precision, n * S, draw, mlp_c, L.mlp_c_bytes, grad_coarse, stream));
+  }
+  return NB_OK;
+}
+
+}  // extern "C"

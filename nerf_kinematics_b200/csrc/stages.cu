@@ -11,7 +11,7 @@
 namespace nb {
 
 thread_local char g_err[512] = "";
-thread_local int64_t g_launches = 0;
+std::atomic<int64_t> g_launches{0};
 
 void set_error(const char* fmt, ...) {
   va_list ap;
@@ -187,8 +187,8 @@ extern "C" {
 
 int nb_abi_version(void) { return NB_ABI_VERSION; }
 const char* nb_last_error(void) { return nb::g_err; }
-int64_t nb_launch_count(void) { return nb::g_launches; }
-void nb_launch_count_reset(void) { nb::g_launches = 0; }
+int64_t nb_launch_count(void) { return nb::g_launches.load(); }
+void nb_launch_count_reset(void) { nb::g_launches.store(0); }
 
 int nb_device_count(void) {
   int n = 0;

@@ -1,0 +1,207 @@
+"""The north_star API surface: create_nerf / render / render_path / render_rays / batchify_rays / run_network.
+
+Semantics follow nerf/run_nerf.py line for line (citations per function); the arithmetic is the CUDA
+library behind include/nerf_b200.h.  Differences a caller can observe, all deliberate:
+  * tensors are torch CUDA tensors instead of TF eager tensors (render_path still returns numpy);
+  * the `focal` position also accepts a 3x3 intrinsics matrix K (yenchenlin-style) -- a scalar gives
+    K = [[f,0,W/2],[0,f,H/2],[0,0,1]], bit-identical to get_rays (run_nerf_helpers.py:123-130);
+  * `chunk` bounds live scratch only; `netchunk` is accepted and ignored (the network kernel tiles
+    internally, "Does not affect final results", run_nerf.py:271-272);
+  * `precision=` ('fp32' | 'bf16') may be passed through render kwargs to pick the kernel family;
+  * NaN guard: TF's check_numerics (run_nerf.py:240-241) is opt-in via check_numerics=True.
+"""
+import os
+import time
+
+import numpy as np
+import torch
+
+from . import ops
+from .models import NeRF
+from .nerf_helpers import get_embedder, to8b
+from .render_core import render_chunk
+
+
+def run_network(inputs, viewdirs, fn, embed_fn=None, embeddirs_fn=None, netchunk=1024 * 64):
+    """run_nerf.py:30-45.  The embedding is fused into the network kernel, so embed_fn / embeddirs_fn /
+    netchunk are accepted for signature compatibility only."""
+    return fn.query(inputs, viewdirs)
+
+
+def render_rays(ray_batch, network_fn, network_query_fn, N_samples, retraw=False, lindisp=False, perturb=0.0,
+                N_importance=0, network_fine=None, white_bkgd=False, raw_noise_std=0.0, verbose=False,
+                precision=None, check_numerics=False, rnd=None):
+    """run_nerf.py:48-243 -> dict(rgb_map, disp_map, acc_map[, raw][, rgb0, disp0, acc0, z_std])."""
+    out = render_chunk(ray_batch, network_fn, network_fine, N_samples=N_samples, N_importance=N_importance,
+                       lindisp=lindisp, perturb=perturb, white_bkgd=white_bkgd, raw_noise_std=raw_noise_std,
+                       precision=precision, rnd=rnd, want_raw=retraw)
+    ret = {"rgb_map": out["rgb"], "disp_map": out["disp"], "acc_map": out["acc"]}
+    if retraw:
+        ret["raw"] = out["raw"]
+    if N_importance > 0:
+        ret["rgb0"], ret["disp0"], ret["acc0"], ret["z_std"] = out["rgb0"], out["disp0"], out["acc0"], out["z_std"]
+    if check_numerics:
+        for k, v in ret.items():
+            if not torch.isfinite(v).all():
+                raise FloatingPointError("output %s : Tensor had NaN or Inf values" % k)
+    return ret
+
+
+def batchify_rays(rays_flat, chunk=1024 * 32, **kwargs):
+    """run_nerf.py:246-257."""
+    all_ret = {}
+    for i in range(0, rays_flat.shape[0], chunk):
+        ret = render_rays(rays_flat[i:i + chunk], **kwargs)
+        for k, v in ret.items():
+            all_ret.setdefault(k, []).append(v)
+    return {k: (torch.cat(v, 0) if len(v) > 1 else v[0]) for k, v in all_ret.items()}
+
+
+def _focal_scalar(K):
+    fx, fy, _, _ = ops.intrinsics(1, 1, K)
+    return fx
+
+
+def render(H, W, focal, chunk=1024 * 32, rays=None, c2w=None, ndc=True, near=0.0, far=1.0, use_viewdirs=False,
+           c2w_staticcam=None, **kwargs):
+    """run_nerf.py:260-336 -> [rgb_map, disp_map, acc_map, extras].  `focal` may be a 3x3 K."""
+    H, W = int(H), int(W)
+    if c2w is not None:
+        rays_o, rays_d = ops.get_rays(H, W, focal, c2w)
+    else:
+        rays_o, rays_d = rays[0], rays[1]
+    viewdir_src = None
+    if use_viewdirs and c2w_staticcam is not None:
+        viewdir_src = rays_d
+        rays_o, rays_d = ops.get_rays(H, W, focal, c2w_staticcam)
+    sh = rays_d.shape
+    near_arr = near if isinstance(near, torch.Tensor) and near.numel() > 1 else None
+    far_arr = far if isinstance(far, torch.Tensor) and far.numel() > 1 else None
+    packed = ops.make_ray_batch(rays_o, rays_d, 0.0 if near_arr is not None else float(near),
+                                0.0 if far_arr is not None else float(far), use_viewdirs=use_viewdirs, ndc=ndc, H=H, W=W,
+                                focal=_focal_scalar(focal), viewdir_src=viewdir_src, near_arr=near_arr, far_arr=far_arr)
+    all_ret = batchify_rays(packed, chunk, **kwargs)
+    for k in all_ret:
+        all_ret[k] = all_ret[k].reshape(list(sh[:-1]) + list(all_ret[k].shape[1:]))
+    k_extract = ["rgb_map", "disp_map", "acc_map"]
+    ret_list = [all_ret[k] for k in k_extract]
+    ret_dict = {k: v for k, v in all_ret.items() if k not in k_extract}
+    return ret_list + [ret_dict]
+
+
+def render_path(render_poses, hwf, chunk, render_kwargs, gt_imgs=None, savedir=None, render_factor=0, verbose=False):
+    """run_nerf.py:339-375 -> (rgbs [M,H,W,3], disps [M,H,W]) as numpy arrays."""
+    H, W, focal = hwf
+    if render_factor != 0:
+        H, W = H // render_factor, W // render_factor
+        focal = focal / render_factor if not hasattr(focal, "shape") or np.ndim(focal) == 0 else _scale_K(focal, render_factor)
+    rgbs, disps = [], []
+    t = time.time()
+    with torch.no_grad():
+        for i, c2w in enumerate(render_poses):
+            if verbose:
+                print(i, time.time() - t)
+                t = time.time()
+            c2w = torch.as_tensor(c2w)[:3, :4]
+            rgb, disp, acc, _ = render(H, W, focal, chunk=chunk, c2w=c2w, **render_kwargs)
+            rgbs.append(rgb.cpu().numpy())
+            disps.append(disp.cpu().numpy())
+            if gt_imgs is not None and render_factor == 0 and verbose:
+                print(-10.0 * np.log10(np.mean(np.square(rgbs[-1] - np.asarray(gt_imgs[i])))))
+            if savedir is not None:
+                _write_png(os.path.join(savedir, "{:03d}.png".format(i)), to8b(rgbs[-1]))
+    return np.stack(rgbs, 0), np.stack(disps, 0)
+
+
+def _scale_K(K, factor):
+    K = np.array(K, dtype=np.float64, copy=True)
+    K[:2, :] /= factor
+    return K
+
+
+def _write_png(path, rgb8):
+    try:
+        from PIL import Image
+        Image.fromarray(rgb8).save(path)
+    except ImportError:  # pragma: no cover
+        np.save(path + ".npy", rgb8)
+
+
+def create_nerf(args, device=None):
+    """run_nerf.py:378-458 -> (render_kwargs_train, render_kwargs_test, start, grad_vars, models)."""
+    device = torch.device(device if device is not None else "cuda")
+    embed_fn, input_ch = get_embedder(args.multires, getattr(args, "i_embed", 0))
+    if getattr(args, "i_embed", 0) == -1:
+        raise NotImplementedError("i_embed=-1 (no positional encoding) is not used by any reference config")
+    input_ch_views, embeddirs_fn = 0, None
+    if args.use_viewdirs:
+        embeddirs_fn, input_ch_views = get_embedder(args.multires_views, getattr(args, "i_embed", 0))
+    skips = [4]
+    model = NeRF(D=args.netdepth, W=args.netwidth, input_ch=input_ch, output_ch=4, skips=skips,
+                 input_ch_views=input_ch_views if args.use_viewdirs else 3, use_viewdirs=args.use_viewdirs).to(device)
+    grad_vars = list(model.parameters())
+    models = {"model": model}
+    model_fine = None
+    if args.N_importance > 0:
+        model_fine = NeRF(D=args.netdepth_fine, W=args.netwidth_fine, input_ch=input_ch, output_ch=4, skips=skips,
+                          input_ch_views=input_ch_views if args.use_viewdirs else 3,
+                          use_viewdirs=args.use_viewdirs).to(device)
+        grad_vars += list(model_fine.parameters())
+        models["model_fine"] = model_fine
+    precision = getattr(args, "precision", "fp32")
+    model.precision = precision
+    if model_fine is not None:
+        model_fine.precision = precision
+
+    def network_query_fn(inputs, viewdirs, network_fn):
+        return run_network(inputs, viewdirs, network_fn, embed_fn=embed_fn, embeddirs_fn=embeddirs_fn,
+                           netchunk=getattr(args, "netchunk", 1024 * 64))
+
+    render_kwargs_train = {
+        "network_query_fn": network_query_fn,
+        "perturb": args.perturb,
+        "N_importance": args.N_importance,
+        "network_fine": model_fine,
+        "N_samples": args.N_samples,
+        "network_fn": model,
+        "use_viewdirs": args.use_viewdirs,
+        "white_bkgd": args.white_bkgd,
+        "raw_noise_std": args.raw_noise_std,
+    }
+    if args.dataset_type != "llff" or args.no_ndc:
+        render_kwargs_train["ndc"] = False
+        render_kwargs_train["lindisp"] = args.lindisp
+    render_kwargs_test = dict(render_kwargs_train)
+    render_kwargs_test["perturb"] = False
+    render_kwargs_test["raw_noise_std"] = 0.0
+
+    start = 0
+    basedir, expname = getattr(args, "basedir", None), getattr(args, "expname", None)
+    ft_path = getattr(args, "ft_path", None)
+    if ft_path is not None and ft_path != "None":
+        ckpts = [ft_path]
+    elif basedir is not None and expname is not None and os.path.isdir(os.path.join(basedir, expname)):
+        d = os.path.join(basedir, expname)
+        ckpts = [os.path.join(d, f) for f in sorted(os.listdir(d))
+                 if ("model_" in f and "fine" not in f and "optimizer" not in f)]
+    else:
+        ckpts = []
+    if len(ckpts) > 0 and not getattr(args, "no_reload", False):
+        ft_weights = ckpts[-1]
+        model.set_weights(list(np.load(ft_weights, allow_pickle=True)))
+        start = int(ft_weights[-10:-4]) + 1
+        if model_fine is not None:
+            ft_weights_fine = "{}_fine_{}".format(ft_weights[:-11], ft_weights[-10:])
+            model_fine.set_weights(list(np.load(ft_weights_fine, allow_pickle=True)))
+    return render_kwargs_train, render_kwargs_test, start, grad_vars, models
+
+
+def save_weights(models, basedir, expname, i):
+    """The np.save half of the TF checkpoint layout (run_nerf.py:835-843): model_{i:06d}.npy, model_fine_{i:06d}.npy."""
+    os.makedirs(os.path.join(basedir, expname), exist_ok=True)
+    for k, net in models.items():
+        path = os.path.join(basedir, expname, "{}_{:06d}.npy".format(k, i))
+        arr = np.empty(len(net.get_weights()), dtype=object)
+        for j, w in enumerate(net.get_weights()):
+            arr[j] = w
+        np.save(path, arr, allow_pickle=True)

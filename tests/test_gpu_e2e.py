@@ -1,0 +1,209 @@
+"""GPU: the reference-facing API end to end (render / run_one_iter_of_nerf / create_nerf / train step)
+against golden renders produced by the reference's own code and against the oracle."""
+import types
+
+import numpy as np
+import pytest
+import torch
+
+from conftest import load_golden, maxdiff
+from oracle import nerf_oracle as O
+
+pytestmark = pytest.mark.gpu
+
+import nerf_kinematics_b200 as nk  # noqa: E402
+from nerf_kinematics_b200 import ops  # noqa: E402
+
+DEV = "cuda"
+NAMES = ("rgb_coarse", "disp_coarse", "acc_coarse", "rgb_fine", "disp_fine", "acc_fine")
+
+
+def _options(use_viewdirs=True, no_ndc=True, near=2.0, far=6.0, chunksize=4096, white=False, num_fine=128):
+    mode = types.SimpleNamespace(chunksize=chunksize, num_coarse=64, num_fine=num_fine, perturb=False, lindisp=False,
+                                 radiance_field_noise_std=0.0, white_background=white)
+    return types.SimpleNamespace(nerf=types.SimpleNamespace(use_viewdirs=use_viewdirs, train=mode, validation=mode),
+                                 dataset=types.SimpleNamespace(no_ndc=no_ndc, near=near, far=far))
+
+
+def _models(name):
+    ck = load_golden(name)
+    mc = nk.model_from_state_dict({k[2:]: v for k, v in ck.items() if k.startswith("c.")}).to(DEV)
+    mf = nk.model_from_state_dict({k[2:]: v for k, v in ck.items() if k.startswith("f.")}).to(DEV)
+    return mc, mf
+
+
+def _check_images(got, g, tol):
+    for nm, im in zip(NAMES, got):
+        ref = g[nm]
+        assert im.shape == ref.shape, nm
+        if nm.startswith("disp"):
+            ok = ~torch.isnan(ref)
+            assert bool((torch.isnan(im.cpu()) == torch.isnan(ref)).all()), nm
+            rel = ((im.cpu()[ok] - ref[ok]).abs() / ref[ok].abs().clamp_min(1.0)).max()
+            assert float(rel) <= tol, (nm, float(rel))
+        else:
+            assert maxdiff(im, ref) <= tol, (nm, maxdiff(im, ref))
+
+
+def test_run_one_iter_of_nerf_lego_checkpoint_fp32():
+    g = load_golden("e2e_lego")
+    mc, mf = _models("ckpt_lego_lowres3")
+    ro, rd = nk.get_ray_bundle(g["H"], g["W"], g["focal"], g["c2w"])
+    with torch.no_grad():
+        got = nk.run_one_iter_of_nerf(g["H"], g["W"], g["focal"], mc, mf, ro, rd, _options(chunksize=200),
+                                      mode="validation")
+    _check_images(got, g, 1e-3)
+
+
+def test_run_one_iter_of_nerf_wheel_ndc_fp32():
+    g = load_golden("e2e_wheel_ndc")
+    mc, mf = _models("ckpt_wheel_robot6")
+    ro, rd = nk.get_ray_bundle(g["H"], g["W"], g["focal"], g["c2w"])
+    with torch.no_grad():
+        got = nk.run_one_iter_of_nerf(g["H"], g["W"], g["focal"], mc, mf, ro, rd,
+                                      _options(no_ndc=False, near=0.0, far=1.0), mode="validation")
+    _check_images(got, g, 1e-3)
+
+
+def test_render_api_tf_semantics_and_chunk_invariance():
+    g = load_golden("e2e_lego")
+    mc, mf = _models("ckpt_lego_lowres3")
+    kw = dict(network_query_fn=None, perturb=0.0, N_importance=128, network_fine=mf, N_samples=64, network_fn=mc,
+              use_viewdirs=True, white_bkgd=False, raw_noise_std=0.0, ndc=False, lindisp=False, near=2.0, far=6.0)
+    with torch.no_grad():
+        rgb, disp, acc, extras = nk.render(g["H"], g["W"], g["focal"], chunk=1024 * 32, c2w=g["c2w"][:3, :4], **kw)
+        rgb2, _, _, _ = nk.render(g["H"], g["W"], g["focal"], chunk=100, c2w=g["c2w"][:3, :4], **kw)
+    assert rgb.shape == (g["H"], g["W"], 3) and disp.shape == (g["H"], g["W"])
+    assert set(extras) == {"rgb0", "disp0", "acc0", "z_std"}
+    assert maxdiff(rgb, g["rgb_fine"]) <= 1e-3 and maxdiff(acc, g["acc_fine"]) <= 1e-3
+    assert maxdiff(extras["rgb0"], g["rgb_coarse"]) <= 1e-3
+    assert torch.equal(rgb, rgb2)  # "chunk ... Does not affect final results" (run_nerf.py:271-272)
+    # rays= form with retraw, K as a matrix, render_path to numpy
+    ro, rd = nk.get_rays(g["H"], g["W"], g["focal"], g["c2w"])
+    K = np.array([[g["focal"], 0, g["W"] / 2], [0, g["focal"], g["H"] / 2], [0, 0, 1]])
+    with torch.no_grad():
+        r3, _, _, ex3 = nk.render(g["H"], g["W"], K, rays=torch.stack([ro.reshape(-1, 3), rd.reshape(-1, 3)]),
+                                  retraw=True, **kw)
+        assert r3.shape == (g["H"] * g["W"], 3) and ex3["raw"].shape == (g["H"] * g["W"], 192, 4)
+        assert torch.equal(r3.reshape(g["H"], g["W"], 3), rgb)
+        rgbs, disps = nk.render_path([g["c2w"], g["c2w"]], (g["H"], g["W"], g["focal"]), 4096, kw)
+    assert rgbs.shape == (2, g["H"], g["W"], 3) and isinstance(rgbs, np.ndarray) and disps.shape == (2, g["H"], g["W"])
+    assert maxdiff(torch.from_numpy(rgbs[1]), g["rgb_fine"]) <= 1e-3
+
+
+def test_depth_at_the_compositing_boundary():
+    g = load_golden("e2e_lego")
+    mc, mf = _models("ckpt_lego_lowres3")
+    ro, rd = nk.get_rays(g["H"], g["W"], g["focal"], g["c2w"])
+    rays = ops.make_ray_batch(ro, rd, 2.0, 6.0, use_viewdirs=True)
+    from nerf_kinematics_b200.render_core import render_chunk
+    with torch.no_grad():
+        out = render_chunk(rays, mc, mf, N_samples=64, N_importance=128, want_z=True)
+    assert maxdiff(out["depth"].reshape(g["H"], g["W"]), g["depth_fine"]) <= 1e-3
+    assert maxdiff(out["z_vals"].reshape(g["H"], g["W"], 192), g["z_fine"]) <= 1e-3
+
+
+def test_create_nerf_and_npy_checkpoint_roundtrip(tmp_path):
+    args = types.SimpleNamespace(multires=10, multires_views=4, i_embed=0, use_viewdirs=True, netdepth=8, netwidth=256,
+                                 netdepth_fine=8, netwidth_fine=256, N_importance=128, N_samples=64, perturb=1.0,
+                                 white_bkgd=True, raw_noise_std=0.0, netchunk=65536, dataset_type="blender",
+                                 no_ndc=False, lindisp=False, basedir=str(tmp_path), expname="exp", ft_path=None,
+                                 no_reload=False)
+    (tmp_path / "exp").mkdir()
+    torch.manual_seed(0)
+    kw_train, kw_test, start, grad_vars, models = nk.create_nerf(args)
+    assert start == 0 and set(models) == {"model", "model_fine"}
+    assert set(kw_train) == {"network_query_fn", "perturb", "N_importance", "network_fine", "N_samples", "network_fn",
+                             "use_viewdirs", "white_bkgd", "raw_noise_std", "ndc", "lindisp"}
+    assert kw_test["perturb"] is False and kw_test["raw_noise_std"] == 0.0
+    assert sum(p.numel() for p in grad_vars) == 2 * 595844
+    from nerf_kinematics_b200.run_nerf import save_weights
+    save_weights(models, str(tmp_path), "exp", 1234)
+    kw2, _, start2, _, models2 = nk.create_nerf(args)
+    assert start2 == 1235
+    for a, b in zip(models["model_fine"].state_dict().values(), models2["model_fine"].state_dict().values()):
+        assert torch.equal(a, b)
+    # the 8x256 graph through the TF-named API against the oracle
+    c2w = O.pose_spherical(30.0, -30.0, 4.0)
+    kw_test.update(near=2.0, far=6.0)
+    with torch.no_grad():
+        rgb, disp, acc, extras = nk.render(16, 16, 22.0, chunk=4096, c2w=c2w[:3, :4], **kw_test)
+        sdc = {k: v.cpu() for k, v in models["model"].state_dict().items()}
+        sdf = {k: v.cpu() for k, v in models["model_fine"].state_dict().items()}
+        ref = O.render_image("tf", sdc, sdf, 16, 16, 22.0, c2w, near=2.0, far=6.0, ndc=False, use_viewdirs=True,
+                             n_coarse=64, n_fine=128, n_freq_xyz=10, n_freq_dir=4, white_bkgd=True)
+    assert maxdiff(rgb, ref["rgb_fine"]) <= 1e-3 and maxdiff(acc, ref["acc_fine"]) <= 1e-3
+    assert maxdiff(extras["rgb0"], ref["rgb_coarse"]) <= 1e-3
+    # network_query_fn stays callable (extract_mesh-style users)
+    pts = torch.rand(5, 7, 3, device=DEV)
+    vd = torch.nn.functional.normalize(torch.randn(5, 3, device=DEV), dim=-1)
+    raw = kw_test["network_query_fn"](pts, vd, models["model"])
+    assert maxdiff(raw, O.run_mlp("tf", sdc, pts.cpu(), vd.cpu(), 10, 4)) <= 1e-4
+
+
+def test_train_step_gradients_match_reference_autograd():
+    g = load_golden("train_flexible")
+    mc = nk.model_from_state_dict(O.init_flexible_state(seed=11)).to(DEV)
+    mf = nk.model_from_state_dict(O.init_flexible_state(seed=12)).to(DEV)
+    rays, tgt = g["rays"].to(DEV), g["target"].to(DEV)
+    opts = _options(white=True)
+    out = nk.predict_and_render_radiance(rays, mc, mf, opts)
+    loss = nk.img2mse(out[0], tgt) + nk.img2mse(out[3], tgt)
+    loss.backward()
+    assert abs(float(loss) - float(g["loss"])) <= 1e-5
+    for pre, m in (("gc.", mc), ("gf.", mf)):
+        for k, p in m.named_parameters():
+            ref = g[pre + k]
+            assert p.grad is not None, k
+            tol = 1e-5 + 1e-3 * float(ref.abs().max())
+            assert maxdiff(p.grad, ref) <= tol, (pre + k, maxdiff(p.grad, ref), float(ref.abs().max()))
+    # an optimizer step through ordinary torch.optim keeps the kernels' flat buffer in sync
+    opt = torch.optim.Adam(list(mc.parameters()) + list(mf.parameters()), lr=5e-3)
+    before = float(loss)
+    for _ in range(5):
+        opt.zero_grad()
+        out = nk.predict_and_render_radiance(rays, mc, mf, opts)
+        loss = nk.img2mse(out[0], tgt) + nk.img2mse(out[3], tgt)
+        loss.backward()
+        opt.step()
+    assert float(loss) < before
+
+
+def test_tf_graph_train_gradients_against_oracle():
+    sdc, sdf = O.init_tf8x256_state(D=4, W=64, skips=(1,), seed=21), O.init_tf8x256_state(D=4, W=64, skips=(1,), seed=22)
+    mc, mf = nk.model_from_state_dict(sdc).to(DEV), nk.model_from_state_dict(sdf).to(DEV)
+    g = load_golden("train_flexible")
+    rays, tgt = g["rays"][:32], g["target"][:32]
+
+    def mlp(kind, sd, x, cx, uv=True):
+        return O.mlp_tf8x256(sd, x, cx, uv, skips=(1,))
+    orig = O.mlp_tf8x256
+    O.mlp_tf8x256 = lambda sd, x, cx, uv=True, skips=(1,): orig(sd, x, cx, uv, skips=(1,))
+    try:
+        loss, gc, gf, _ = O.train_step_grads("tf", sdc, sdf, rays, tgt, n_coarse=64, n_fine=128, n_freq_xyz=10,
+                                             n_freq_dir=4, white_bkgd=False)
+    finally:
+        O.mlp_tf8x256 = orig
+    from nerf_kinematics_b200.render_core import render_chunk
+    out = render_chunk(rays.to(DEV), mc, mf, N_samples=64, N_importance=128)
+    l2 = nk.img2mse(out["rgb0"], tgt.to(DEV)) + nk.img2mse(out["rgb"], tgt.to(DEV))
+    l2.backward()
+    assert abs(float(l2) - float(loss)) <= 1e-5
+    for k, p in mc.named_parameters():
+        assert maxdiff(p.grad, gc[k]) <= 1e-5 + 1e-3 * float(gc[k].abs().max()), k
+    for k, p in mf.named_parameters():
+        assert maxdiff(p.grad, gf[k]) <= 1e-5 + 1e-3 * float(gf[k].abs().max()), k
+
+
+def test_bf16_render_within_stated_bound():
+    """bf16 tcgen05 MLP path: <= 1e-2 max-abs on rgb/acc and <= 0.05 dB PSNR delta vs the fp32 render."""
+    g = load_golden("e2e_lego")
+    mc, mf = _models("ckpt_lego_lowres3")
+    ro, rd = nk.get_ray_bundle(g["H"], g["W"], g["focal"], g["c2w"])
+    with torch.no_grad():
+        got = nk.run_one_iter_of_nerf(g["H"], g["W"], g["focal"], mc, mf, ro, rd, _options(), mode="validation",
+                                      precision="bf16")
+    assert maxdiff(got[3], g["rgb_fine"]) <= 1e-2 and maxdiff(got[5], g["acc_fine"]) <= 1e-2
+    tgt = torch.rand(g["H"], g["W"], 3, generator=torch.Generator().manual_seed(0))
+    psnr = lambda im: -10 * torch.log10(torch.mean((im.cpu() - tgt) ** 2))
+    assert abs(float(psnr(got[3]) - psnr(g["rgb_fine"]))) <= 0.05

@@ -1,0 +1,68 @@
+"""GPU: the MLP kernels (fp32 FFMA path and bf16 tcgen05 path) against the oracle graphs."""
+import pytest
+import torch
+
+from conftest import load_golden, maxdiff
+from oracle import nerf_oracle as O
+
+pytestmark = pytest.mark.gpu
+
+import nerf_kinematics_b200 as nk  # noqa: E402
+
+DEV = "cuda"
+
+
+def _pts(n, S, seed):
+    g = torch.Generator().manual_seed(seed)
+    pts = (torch.rand(n, S, 3, generator=g) * 2 - 1) * 3.0
+    dirs = torch.nn.functional.normalize(torch.randn(n, 3, generator=g), dim=-1)
+    return pts, dirs
+
+
+def test_flexible_fp32_against_reference_checkpoint_output():
+    g = load_golden("mlp_flexible")
+    ck = load_golden("ckpt_lego_lowres3")
+    m = nk.model_from_state_dict({k[2:]: v for k, v in ck.items() if k.startswith("c.")}).to(DEV)
+    raw = m.query(g["pts"].to(DEV)[:, None, :], g["dirs"].to(DEV))
+    assert raw.shape == (200, 1, 4)
+    assert maxdiff(raw[:, 0], g["raw"]) <= 2e-4  # fp32 FFMA vs the reference's fp32 GEMM; pre-activations reach ~30
+
+
+@pytest.mark.parametrize("kind", ["flexible", "tf"])
+@pytest.mark.parametrize("uv", [True, False])
+def test_fp32_graphs_against_oracle(kind, uv):
+    pts, dirs = _pts(37, 13, 4)
+    if kind == "flexible":
+        sd = O.init_flexible_state(seed=2)
+        if not uv:
+            sd = {k: v for k, v in sd.items() if k.startswith(("layer1", "layers_xyz"))}
+            sd["fc_out.weight"], sd["fc_out.bias"] = torch.randn(4, 128) * 0.1, torch.randn(4) * 0.1
+        ref = O.run_mlp("flexible", sd, pts, dirs if uv else None, 10, 4)
+    else:
+        sd = O.init_tf8x256_state(use_viewdirs=uv, seed=3)
+        ref = O.run_mlp("tf", sd, pts, dirs if uv else None, 10, 4)
+    m = nk.model_from_state_dict(sd).to(DEV)
+    got = m.query(pts.to(DEV), dirs.to(DEV) if uv else None)
+    assert maxdiff(got, ref) <= 1e-4
+
+
+def test_tf_graph_small_widths_and_depths():
+    pts, dirs = _pts(9, 5, 7)
+    sd = O.init_tf8x256_state(D=6, W=64, seed=5)
+    # the bottleneck is Dense(256) whatever W is (run_nerf_helpers.py:104)
+    assert sd["bottleneck_linear.weight"].shape == (256, 64)
+    ref = O.run_mlp("tf", sd, pts, dirs, 10, 4)
+    got = nk.model_from_state_dict(sd).to(DEV).query(pts.to(DEV), dirs.to(DEV))
+    assert maxdiff(got, ref) <= 1e-4
+
+
+def test_bf16_tensor_core_path_against_fp32_oracle():
+    pts, dirs = _pts(300, 64, 11)
+    for kind, sd in (("tf", O.init_tf8x256_state(seed=0)), ("flexible", O.init_flexible_state(seed=1))):
+        ref = O.run_mlp(kind, sd, pts, dirs, 10, 4)
+        m = nk.model_from_state_dict(sd).to(DEV)
+        m.precision = "bf16"
+        got = m.query(pts.to(DEV), dirs.to(DEV))
+        err = maxdiff(got, ref)
+        scale = float(ref.abs().max())
+        assert err <= 2e-2 * max(1.0, scale), (kind, err, scale)
