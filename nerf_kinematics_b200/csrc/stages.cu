@@ -203,10 +203,11 @@ int nb_device_count(void) {
 
 int nb_get_rays(int H, int W, float fx, float fy, float cx, float cy, const float* c2w, int row0, int row1,
                 float* rays_o, float* rays_d, nb_stream_t stream) {
-  NB_REQUIRE(H > 0 && W > 0 && c2w && rays_o && rays_d, "nb_get_rays: bad arguments");
+  NB_REQUIRE(H > 0 && W > 0 && c2w, "nb_get_rays: bad arguments");
   NB_REQUIRE(0 <= row0 && row0 <= row1 && row1 <= H, "nb_get_rays: rows [%d,%d) outside image height %d", row0, row1, H);
   int64_t n = (int64_t)(row1 - row0) * W;
   if (n == 0) return NB_OK;
+  NB_REQUIRE(rays_o && rays_d, "nb_get_rays: null output");
   Cam cam;
   memcpy(cam.r, c2w, sizeof(cam.r));
   get_rays_kernel<<<(unsigned)ceil_div(n, 256), 256, 0, as_stream(stream)>>>(W, fx, fy, cx, cy, cam, row0, n, rays_o, rays_d);

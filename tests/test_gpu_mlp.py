@@ -25,7 +25,9 @@ def test_flexible_fp32_against_reference_checkpoint_output():
     m = nk.model_from_state_dict({k[2:]: v for k, v in ck.items() if k.startswith("c.")}).to(DEV)
     raw = m.query(g["pts"].to(DEV)[:, None, :], g["dirs"].to(DEV))
     assert raw.shape == (200, 1, 4)
-    assert maxdiff(raw[:, 0], g["raw"]) <= 2e-4  # fp32 FFMA vs the reference's fp32 GEMM; pre-activations reach ~30
+    # the seeded points lie outside the trained volume, raw reaches ~5e3: compare relative to magnitude
+    rel = (raw[:, 0].cpu() - g["raw"]).abs() / g["raw"].abs().clamp_min(1.0)
+    assert float(rel.max()) <= 1e-5
 
 
 @pytest.mark.parametrize("kind", ["flexible", "tf"])
