@@ -49,6 +49,7 @@ def main():
     ap.add_argument("--rays", type=int, default=32768)
     ap.add_argument("--reps", type=int, default=10)
     ap.add_argument("--model", default="tf", choices=["tf", "flexible"])
+    ap.add_argument("--only-mlp", action="store_true", help="just the 16-bit fused MLP kernel (short run for ncu)")
     a = ap.parse_args()
     pk = peaks()
     dev = torch.device("cuda:0")
@@ -60,10 +61,10 @@ def main():
     rays = ops.make_ray_batch(o, d, 2.0, 6.0, use_viewdirs=True)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)  # > 126 MB L2
     res = {}
-    for S_ in (S, S + I):
+    for S_ in ((S + I,) if a.only_mlp else (S, S + I)):
         z = ops.sample_coarse(rays, S_)
         raw = torch.empty(n, S_, 4, device=dev)
-        for prec_name in ("bf16", "fp32"):
+        for prec_name in (("bf16",) if a.only_mlp else ("bf16", "fp32")):
             h, prec = model.prepare(prec_name)
             P = n * S_
             if prec_name == "fp32" and P > (1 << 21):
@@ -80,7 +81,13 @@ def main():
             print("mlp_forward %-4s %s S=%3d  P=%9d  %8.3f ms  %8.1f TFLOP/s  frac(of measured bf16 %.0f)=%.3f  [best %.3f ms]"
                   % (prec_name, a.model, S_, P, med * 1e3, tf, pk["bf16_tflops"], tf / pk["bf16_tflops"], best * 1e3))
             res["mlp_%s_%d" % (prec_name, S_)] = tf
-    # HBM-bound stages
+    if a.only_mlp:
+        return
+    # HBM-bound stages (use >= 1M rays so the kernels run long enough to measure bandwidth)
+    n = max(n, 1 << 20)
+    o = torch.randn(n, 3, device=dev) * 0.5 + torch.tensor([0, 0, 4.0], device=dev)
+    d = torch.nn.functional.normalize(torch.randn(n, 3, device=dev), dim=-1)
+    rays = ops.make_ray_batch(o, d, 2.0, 6.0, use_viewdirs=True)
     for S_, tag in ((S, "coarse"), (S + I, "fine")):
         z = ops.sample_coarse(rays, S_)
         raw = torch.randn(n, S_, 4, device=dev)
