@@ -139,6 +139,12 @@ int nb_mlp_forward_points(const nb_model_t* m, int precision, const float* pts, 
  * ACCUMULATED into.  No gradient is produced for points / rays (nothing trainable upstream). */
 int nb_mlp_backward(const nb_model_t* m, int precision, int64_t n_points, float* d_raw, void* workspace,
                     size_t workspace_bytes, float* flat_grad, nb_stream_t stream);
+/* Introspection of the tensor-core train workspace (NB_PREC_BF16, save_for_backward): byte offsets, from
+ * `workspace`, of the per-tile X record (forward operand tiles: [encx, encd, activations of every stage]) and dZ record
+ * (gradient tiles in dgrad-chain order), and their sizes in 16 KB blocks (128 points x 64 fp16, SWIZZLE_128B image)
+ * per 128-point tile.  Used by the parity tests to check dgrad / wgrad exactly against the saved activations. */
+int nb_mlp_record_layout(const nb_model_t* m, int64_t n_points, const void* workspace, int64_t* xrec_offset,
+                         int* xrec_blocks, int64_t* drec_offset, int* drec_blocks);
 
 /* ---------------------------------------------------------------- a9 compositing
  * raw2outputs (TF run_nerf.py:93-163) == volume_render_radiance_field (PT volume_rendering_utils.py:6-53).

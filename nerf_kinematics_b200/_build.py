@@ -24,6 +24,7 @@ SOURCES = [
     ("model.cu", []),
     ("mlp_fp32.cu", []),
     ("mlp_tc.cu", []),
+    ("mlp_tc_bwd.cu", []),
     ("render.cu", ["--fmad=false"]),
 ]
 

@@ -23,75 +23,12 @@
 //   * the skip concat ([pts, h], K = 64 + 256) and the view-direction concat ([feat, dirs]) are extra
 //     K-blocks fed from the resident encoding tiles, not copies; alpha (N=1) rides along the
 //     bottleneck / fc_feat GEMM as extra output columns; rgb is an N=16 MMA.
-#include <cuda_bf16.h>
-#include <math.h>
-
 #include <algorithm>
 #include <vector>
 
-#include "model.h"
+#include "tc_common.cuh"
 
 namespace nb {
-
-constexpr int kMaxStages = 14;
-constexpr int kMaxKB = 6;
-constexpr int kRing = 3;
-constexpr int kTileM = 128;
-constexpr int kBlockBytes = kTileM * 128;  // one 128-row x 64-element bf16 K-block, SWIZZLE_128B
-enum { SRC_ENCX = 4, SRC_ENCD = 5 };
-enum { EPI_HIDDEN = 0, EPI_HEAD = 1, EPI_RGB = 2, EPI_OUT4 = 3 };
-constexpr int kThreadsTc = 192;
-
-struct TcStage {
-  int n_kb;
-  int a_src[kMaxKB];  // 0..3 activation block, SRC_ENCX, SRC_ENCD
-  int n_main;         // N of the main MMA (multiple of 16, <= 256)
-  int n_extra;        // 0 | 16: second MMA on chunk rows [n_main, n_main+16) -> other accumulator buffer, col 0
-  int chunk_bytes;    // (n_main + n_extra) * 128
-  int w_off;          // byte offset of K-block 0 in the packed weights; K-block k at w_off + k*chunk_bytes
-  int b_off;          // float offset of this stage's biases
-  int epi, relu;
-  int n_act;          // columns stored back as activations (multiple of 64)
-  int alpha_col;      // EPI_HEAD: accumulator column of alpha in this stage's buffer, -1 = other buffer col 0
-};
-
-struct TcPlan {
-  int n_stages, n_act_blocks, Cx, Cd, Lx, Ld, n_bias, ring_stage_bytes;
-  TcStage st[kMaxStages];
-};
-
-struct PackSeg {
-  long long dst_off;  // bytes, start of the chunk in the packed image
-  long long src_off;  // floats, start of the source matrix in the flat parameters
-  int row0, n_rows;   // chunk rows [row0, row0+n_rows) <- source rows [0, n_rows)
-  int ld, col0, ncols;  // source leading dim; chunk element k <- source column col0+k for k < ncols, else 0
-};
-struct BiasSeg {
-  int dst, count;
-  long long src_off;
-};
-
-struct PackedBf16 {
-  TcPlan plan;
-  unsigned char* d_w = nullptr;
-  float* d_bias = nullptr;
-  PackSeg* d_segs = nullptr;
-  BiasSeg* d_bsegs = nullptr;
-  int n_segs = 0, n_bsegs = 0;
-  size_t w_bytes = 0;
-  size_t smem_bytes = 0;
-  bool supported = false;
-};
-
-// Forward operands are IEEE fp16 (tcgen05 kind::f16 takes f16 or bf16 at the same rate): 11 significand bits keep
-// the rendered image ~5x closer to the fp32 reference than bf16 does (measured: 2.2e-3 vs 1.07e-2 max-abs on the
-// lego checkpoint); conversions saturate at +-65504 instead of overflowing to inf.  Element 2i sits in the low half.
-__device__ __forceinline__ uint32_t pack_h2(float lo, float hi, bool relu) {
-  uint32_t d;
-  if (relu) asm("cvt.rn.relu.satfinite.f16x2.f32 %0, %1, %2;" : "=r"(d) : "f"(hi), "f"(lo));
-  else asm("cvt.rn.satfinite.f16x2.f32 %0, %1, %2;" : "=r"(d) : "f"(hi), "f"(lo));
-  return d;
-}
 
 // ------------------------------------------------------------------------------------ weight packing
 __global__ void pack_weights_kernel(const float* __restrict__ params, const PackSeg* __restrict__ segs,
@@ -122,89 +59,6 @@ __global__ void pack_bias_kernel(const float* __restrict__ params, const BiasSeg
   for (int i = threadIdx.x; i < sg.count; i += blockDim.x) out[sg.dst + i] = params[sg.src_off + i];
 }
 
-// ------------------------------------------------------------------------------------ PTX wrappers
-__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
-
-__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
-  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count));
-}
-__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
-  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
-}
-__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
-  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
-}
-__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
-  asm volatile(
-      "{\n"
-      ".reg .pred P1;\n"
-      "WAIT_LOOP:\n"
-      "mbarrier.try_wait.parity.shared::cta.b64 P1, [%0], %1;\n"
-      "@P1 bra DONE;\n"
-      "bra WAIT_LOOP;\n"
-      "DONE:\n"
-      "}\n" ::"r"(bar),
-      "r"(parity)
-      : "memory");
-}
-__device__ __forceinline__ void bulk_g2s(uint32_t dst, const void* src, uint32_t bytes, uint32_t bar) {
-  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst),
-               "l"(src), "r"(bytes), "r"(bar)
-               : "memory");
-}
-__device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
-__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
-__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
-__device__ __forceinline__ void tc_commit(uint32_t bar) {
-  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
-}
-__device__ __forceinline__ void tc_mma(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc, uint32_t acc) {
-  asm volatile(
-      "{\n"
-      ".reg .pred p;\n"
-      "setp.ne.b32 p, %4, 0;\n"
-      "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n"
-      "}\n" ::"r"(d_tmem),
-      "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(acc)
-      : "memory");
-}
-__device__ __forceinline__ void tc_wait_ld() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
-
-#define NB_TMEM_LD32(taddr, v)                                                                                      \
-  asm volatile(                                                                                                     \
-      "tcgen05.ld.sync.aligned.32x32b.x32.b32 "                                                                     \
-      "{%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16,%17,%18,%19,%20,%21,%22,%23,%24,%25,%26,%27,%28," \
-      "%29,%30,%31}, [%32];"                                                                                        \
-      : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]), \
-        "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]), "=r"(v[16]),      \
-        "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]), "=r"(v[24]),     \
-        "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])                   \
-      : "r"(taddr))
-
-__device__ __forceinline__ void tmem_ld4(uint32_t taddr, uint32_t (&v)[4]) {
-  asm volatile("tcgen05.ld.sync.aligned.32x32b.x4.b32 {%0,%1,%2,%3}, [%4];"
-               : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3])
-               : "r"(taddr));
-}
-__device__ __forceinline__ uint32_t tmem_ld1(uint32_t taddr) {
-  uint32_t v;
-  asm volatile("tcgen05.ld.sync.aligned.32x32b.x1.b32 {%0}, [%1];" : "=r"(v) : "r"(taddr));
-  return v;
-}
-
-// UMMA shared-memory descriptor: K-major operand, SWIZZLE_128B, 8-row groups 1024 B apart (SBO), version 1.
-__device__ __forceinline__ uint64_t umma_desc(uint32_t saddr) {
-  uint64_t d = (uint64_t)((saddr & 0x3FFFFu) >> 4);
-  d |= (uint64_t)1 << 16;            // leading byte offset (unused for swizzled K-major), 16 B units
-  d |= (uint64_t)(1024 >> 4) << 32;  // stride byte offset
-  d |= (uint64_t)1 << 46;            // descriptor version (sm_100)
-  d |= (uint64_t)2 << 61;            // SWIZZLE_128B
-  return d;
-}
-// Instruction descriptor kind::f16: D=f32 (bit 4), A/B format 0 = f16 (1 would be bf16), both K-major, M=128.
-__device__ __forceinline__ uint32_t umma_idesc(int n) {
-  return (1u << 4) | (0u << 7) | (0u << 10) | ((uint32_t)(n >> 3) << 17) | ((uint32_t)(kTileM >> 4) << 24);
-}
 
 
 // ------------------------------------------------------------------------------------ point source
@@ -256,7 +110,7 @@ __device__ __forceinline__ void encode_row(unsigned char* block, int row, float 
 // ------------------------------------------------------------------------------------ the kernel
 __global__ void __launch_bounds__(kThreadsTc, 1)
 mlp_tc_kernel(const __grid_constant__ TcPlan plan, const unsigned char* __restrict__ wpk, const float* __restrict__ bias_g,
-              TcSrc src, long long n_points, float* __restrict__ raw) {
+              TcSrc src, long long n_points, float* __restrict__ raw, unsigned char* __restrict__ rec) {
   extern __shared__ __align__(1024) unsigned char smem_raw[];
   // carve (all tile regions 1024-byte aligned for SWIZZLE_128B)
   unsigned char* smem = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
@@ -327,6 +181,14 @@ mlp_tc_kernel(const __grid_constant__ TcPlan plan, const unsigned char* __restri
         mbar_wait(smem_u32(bar_enc), enc_phase);
         enc_phase ^= 1;
         tc_fence_after();
+        // train: every operand tile is also written to the per-tile X record, in the exact swizzled image the
+        // backward kernels load (K-major for recompute-free dgrad masks, MN-major operand of the wgrad MMAs)
+        unsigned char* rec_tile = rec ? rec + (size_t)tile * plan.rec_blocks * kBlockBytes : nullptr;
+        if (rec_tile) {
+          bulk_s2g(rec_tile, smem_u32(encx), kBlockBytes);
+          if (plan.Cd > 0) bulk_s2g(rec_tile + kBlockBytes, smem_u32(encd), kBlockBytes);
+          bulk_commit();
+        }
         for (int s = 0; s < plan.n_stages; ++s) {
           const TcStage& st = plan.st[s];
           const int buf = s & 1;
@@ -342,6 +204,10 @@ mlp_tc_kernel(const __grid_constant__ TcPlan plan, const unsigned char* __restri
               act_phase[sidx] ^= 1;
               tc_fence_after();
               a_base = smem_u32(act + sidx * kBlockBytes);
+              if (rec_tile) {
+                bulk_s2g(rec_tile + (size_t)(plan.st[s - 1].rec_blk + sidx) * kBlockBytes, a_base, kBlockBytes);
+                bulk_commit();
+              }
             } else {
               a_base = smem_u32(sidx == SRC_ENCX ? encx : encd);
             }
@@ -359,9 +225,11 @@ mlp_tc_kernel(const __grid_constant__ TcPlan plan, const unsigned char* __restri
             tc_commit(smem_u32(bar_empty + slot));  // frees the ring slot when these MMAs have read it
             if (++slot == kRing) { slot = 0; phase ^= 1; }
           }
+          if (rec_tile) bulk_wait_read0();     // record stores have read the tiles this stage's epilogue overwrites
           tc_commit(smem_u32(bar_acc + buf));  // accumulator of this stage complete
         }
       }
+      if (rec) bulk_wait0();
     }
   } else {
     // ============================ epilogue warps (thread == row) ============================
@@ -467,6 +335,7 @@ mlp_tc_kernel(const __grid_constant__ TcPlan plan, const unsigned char* __restri
 // ------------------------------------------------------------------------------------ host: plan + packing
 void packed_free(PackedBf16* p) {
   if (p == nullptr) return;
+  bw_free(p);
   cudaFree(p->d_w);
   cudaFree(p->d_bias);
   cudaFree(p->d_segs);
@@ -485,6 +354,7 @@ static bool build_plan(const Graph& g, TcPlan& plan, std::vector<PackSeg>& segs,
   const int wb = g.width / 64;
   plan.n_act_blocks = std::max(wb, g.use_viewdirs ? g.feat_width / 64 : 0);
   plan.Cx = g.Cx; plan.Cd = g.Cd; plan.Lx = g.n_freq_xyz; plan.Ld = g.n_freq_dir;
+  plan.rec_blocks = 2;  // [encx, encd]
   size_t woff = 0;
   int boff = 0, ring_max = 0;
   auto begin_stage = [&](int n_main, int n_extra, int epi, int relu, int n_act, int alpha_col) -> TcStage& {
@@ -492,6 +362,8 @@ static bool build_plan(const Graph& g, TcPlan& plan, std::vector<PackSeg>& segs,
     st.n_kb = 0;
     st.n_main = n_main; st.n_extra = n_extra; st.chunk_bytes = (n_main + n_extra) * 128;
     st.w_off = (int)woff; st.b_off = boff; st.epi = epi; st.relu = relu; st.n_act = n_act; st.alpha_col = alpha_col;
+    st.rec_blk = plan.rec_blocks;
+    plan.rec_blocks += n_act / 64;
     boff += (n_main + n_extra + 3) & ~3;
     ring_max = std::max(ring_max, st.chunk_bytes);
     return st;
@@ -607,8 +479,11 @@ int packed_build(nb_model* m, cudaStream_t stream) {
       return NB_ERR_CUDA;
     }
     m->packed = p;
+    int rc = bw_setup(m, stream);
+    if (rc != NB_OK) return rc;
   }
   PackedBf16* p = m->packed;
+  p->wt_fresh = false;  // the transposed images are rebuilt by the next backward call
   int max_rows = 0;
   // one launch over all segments; blockIdx.x covers the largest segment
   max_rows = 272;
@@ -620,32 +495,39 @@ int packed_build(nb_model* m, cudaStream_t stream) {
   return NB_OK;
 }
 
-size_t tc_workspace_bytes(const nb_model*, int64_t, int) { return 0; }
+size_t tc_workspace_bytes(const nb_model* m, int64_t n_points, int save_for_backward) {
+  if (!save_for_backward || m->packed == nullptr || !m->packed->bw_supported) return 0;
+  return tc_train_workspace_bytes(m->packed, n_points);
+}
 
 int tc_forward(const nb_model* m, const float* rays, int ray_stride, const float* z_vals, const float* pts,
                const float* viewdirs, int points_per_dir, int64_t n_rays, int n_samples, int64_t n_points, float* raw,
-               void*, size_t, int save_for_backward, cudaStream_t stream) {
+               void* ws, size_t ws_bytes, int save_for_backward, cudaStream_t stream) {
   (void)n_rays;
   if (m->packed == nullptr) {
     set_error("nb_mlp_forward: nb_model_pack(NB_PREC_BF16) has not been called");
     return NB_ERR_INVALID;
   }
-  if (save_for_backward) {
-    set_error("bf16 tensor-core path: backward is not available yet, train with NB_PREC_FP32");
-    return NB_ERR_UNSUPPORTED;
-  }
   const PackedBf16* p = m->packed;
+  unsigned char* rec = nullptr;
+  if (save_for_backward) {
+    if (!p->bw_supported) {
+      set_error("tensor-core backward does not support this graph (train it with NB_PREC_FP32)");
+      return NB_ERR_UNSUPPORTED;
+    }
+    const size_t need = tc_train_workspace_bytes(p, n_points);
+    if (ws == nullptr || ws_bytes < need) {
+      set_error("nb_mlp_forward: workspace of %zu bytes given, %zu needed", ws_bytes, need);
+      return NB_ERR_WORKSPACE;
+    }
+    rec = tc_train_xrec(p, ws, n_points);
+  }
   TcSrc src{rays, ray_stride, z_vals, n_samples > 0 ? n_samples : 1, pts, viewdirs, points_per_dir > 0 ? points_per_dir : 1};
   const int64_t n_tiles = ceil_div(n_points, kTileM);
   const int grid = (int)std::min<int64_t>(n_tiles, sm_count());
-  mlp_tc_kernel<<<grid, kThreadsTc, p->smem_bytes, stream>>>(p->plan, p->d_w, p->d_bias, src, (long long)n_points, raw);
+  mlp_tc_kernel<<<grid, kThreadsTc, p->smem_bytes, stream>>>(p->plan, p->d_w, p->d_bias, src, (long long)n_points, raw, rec);
   NB_LAUNCHED();
   return NB_OK;
-}
-
-int tc_backward(const nb_model*, int64_t, float*, void*, size_t, float*, cudaStream_t) {
-  set_error("bf16 tensor-core path: backward is not available yet, train with NB_PREC_FP32");
-  return NB_ERR_UNSUPPORTED;
 }
 
 }  // namespace nb
