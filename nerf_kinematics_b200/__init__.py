@@ -14,3 +14,4 @@ from .train_utils import predict_and_render_radiance, run_one_iter_of_nerf  # no
 from .volume_rendering_utils import volume_render_radiance_field  # noqa: F401
 
 __version__ = "0.1.0"
+BF16_BACKWARD = True  # the tensor-core path has a backward (csrc/mlp_tc_bwd.cu): bench.py trains with it

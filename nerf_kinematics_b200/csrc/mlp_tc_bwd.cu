@@ -8,7 +8,7 @@
 //   * ReLU masks of the dgrad chain (x > 0 element-wise, same swizzled position as the gradient element),
 //   * MN-major operand of the wgrad MMAs (contraction over the 128 points = the ROWS of a block).
 //
-// Three kernels:
+// Two kernels:
 //   1. mlp_tc_dgrad_kernel -- the reversed layer chain for a tile, fused exactly like the forward: dZ tiles stay in
 //      shared memory / TMEM between layers; A = dZ (K-major), B = transposed weight chunks streamed through a ring
 //      by bulk async copies, D in TMEM; epilogue = tcgen05.ld -> ReLU mask -> fp16 -> next A operand.  Each dZ tile is
@@ -17,10 +17,12 @@
 //      records, accumulators resident in TMEM (up to 256x256 fp32 = all 512 columns) while a CTA sweeps its slice of
 //      the points (split-K over CTAs), bias gradients as column sums by otherwise idle warps; partial results are
 //      reduced deterministically by wgrad_reduce_kernel into the caller's flat gradient.
-//   3. head_grad_kernel -- the N_out <= 4 heads (rgb / alpha / output_linear) in SIMT fp32.
+//      The N_out <= 4 heads (rgb / alpha / output_linear) are wgrad units too: their dZ is the scaled 16-bit d_raw tile.
 //
 // Gradients are computed in fp16 with a per-call power-of-two scale chosen from max|d_raw| (absmax_kernel), so the
 // 5-bit exponent is centred on the data; the scale is removed in fp32 by the reduce kernel.
+#include <stdlib.h>
+
 #include <algorithm>
 #include <vector>
 
@@ -31,7 +33,7 @@ namespace nb {
 constexpr int kThreadsBw = 224;   // W producer, MMA issuer, 4 epilogue warps, mask producer
 constexpr int kMaskRing = 3;
 constexpr int kThreadsWg = 192;   // producer, MMA issuer, 4 column-sum / epilogue warps
-constexpr int kWgStages = 3;
+constexpr int kWgMaxStages = 8;
 constexpr int kHalfBytes = 64 * 128;  // 64 points of a block
 
 // scale = 2^floor(log2(1024 / max|d_raw|)); 1 when the maximum is 0 or not finite
@@ -127,6 +129,8 @@ mlp_tc_dgrad_kernel(const __grid_constant__ BwPlan plan, const BwArgs a) {
     asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "r"(512));
     asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
   }
+  // columns 8..63 of the d_raw tile are never written again: zero them once (they are rows of an MN-major wgrad operand)
+  for (int i = threadIdx.x; i < kBlockBytes / 16; i += blockDim.x) reinterpret_cast<uint4*>(draw)[i] = make_uint4(0u, 0u, 0u, 0u);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -179,6 +183,8 @@ mlp_tc_dgrad_kernel(const __grid_constant__ BwPlan plan, const BwArgs a) {
         mbar_wait(smem_u32(bar_draw), draw_phase);
         draw_phase ^= 1;
         tc_fence_after();
+        bulk_s2g(dt + (size_t)plan.draw_blk * kBlockBytes, smem_u32(draw), kBlockBytes);
+        bulk_commit();
         for (int s = 0; s < plan.n_stages; ++s) {
           const BwStage& st = plan.st[s];
           const int buf = s & 1;
@@ -303,6 +309,12 @@ mlp_tc_dgrad_kernel(const __grid_constant__ BwPlan plan, const BwArgs a) {
 }
 
 // ------------------------------------------------------------------------------------ wgrad (split-K over CTAs)
+// pipeline depth of a unit whose stage holds n_slots half-blocks: as many as fit next to the barriers
+__host__ __device__ inline int wg_stages(int n_slots) {
+  const int s = (216 * 1024) / (n_slots * kHalfBytes);
+  return s > kWgMaxStages ? kWgMaxStages : s;
+}
+
 struct WgArgs {
   const unsigned char* xrec;
   const unsigned char* drec;
@@ -311,6 +323,7 @@ struct WgArgs {
   long long n_tiles;
   int rec_blocks, drec_blocks;
   int part0[kMaxUnits + 1];  // CTA b works on unit u with part0[u] <= b < part0[u+1]
+  int dbg;                   // NB_WG_DEBUG bit 0: no loads, bit 1: no MMAs, bit 2: no column sums (timing experiments)
 };
 constexpr int kPartFloats = 65536;
 
@@ -325,12 +338,13 @@ mlp_tc_wgrad_kernel(const __grid_constant__ WgPlan plan, const __grid_constant__
   const long long tile0 = a.n_tiles * part / nparts, tile1 = a.n_tiles * (part + 1) / nparts;
   const int n_slots = u.m_blocks + u.n_x;
   const int stage_bytes = n_slots * kHalfBytes;
+  const int kWgStages = wg_stages(n_slots);
   const int Ntot = 64 * u.n_x;
   unsigned char* stages = smem;
   uint64_t* bars = reinterpret_cast<uint64_t*>(stages + kWgStages * stage_bytes);
   uint64_t* bar_full = bars;
-  uint64_t* bar_empty = bars + kWgStages;
-  uint64_t* bar_done = bars + 2 * kWgStages;
+  uint64_t* bar_empty = bars + kWgMaxStages;
+  uint64_t* bar_done = bars + 2 * kWgMaxStages;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bar_done + 1);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 
@@ -371,6 +385,7 @@ mlp_tc_wgrad_kernel(const __grid_constant__ WgPlan plan, const __grid_constant__
         const unsigned char* xt = a.xrec + (size_t)tile * a.rec_blocks * kBlockBytes + hoff;
         mbar_wait(smem_u32(bar_empty + slot), phase ^ 1);
         const uint32_t fb = smem_u32(bar_full + slot);
+        if (a.dbg & 1) { mbar_arrive(fb); if (++slot == kWgStages) { slot = 0; phase ^= 1; } continue; }
         mbar_expect_tx(fb, (uint32_t)((u.m_load + u.n_x) * kHalfBytes));
         const uint32_t sbase = smem_u32(stages + slot * stage_bytes);
         for (int b = 0; b < u.m_load; ++b) bulk_g2s(sbase + b * kHalfBytes, dzt + (size_t)b * kBlockBytes, kHalfBytes, fb);
@@ -389,7 +404,7 @@ mlp_tc_wgrad_kernel(const __grid_constant__ WgPlan plan, const __grid_constant__
         tc_fence_after();
         const uint32_t sbase = smem_u32(stages + slot * stage_bytes);
         const uint32_t xb = sbase + u.m_blocks * kHalfBytes;
-        for (int mh = 0; mh < u.m_blocks / 2; ++mh) {
+        for (int mh = 0; mh < ((a.dbg & 2) ? 0 : u.m_blocks / 2); ++mh) {
           const uint32_t ab = sbase + 2 * mh * kHalfBytes;
           const uint32_t d = tmem_base + mh * Ntot;
 #pragma unroll
@@ -409,7 +424,7 @@ mlp_tc_wgrad_kernel(const __grid_constant__ WgPlan plan, const __grid_constant__
     // ---- bias gradient: column sums of the dZ tiles while they sit in shared memory
     const int t = threadIdx.x - 64;
     const int blk = t >> 5, chunk = (t & 31) >> 2, within = (t & 3) * 4;
-    const bool active = u.b_off >= 0 && blk < u.m_load;
+    const bool active = u.b_off >= 0 && blk < u.m_load && !(a.dbg & 4);
     float s0 = 0.0f, s1 = 0.0f;
     uint32_t slot = 0, phase = 0;
     for (long long it = 0; it < n_steps; ++it) {
@@ -474,90 +489,17 @@ __global__ void wgrad_reduce_kernel(const __grid_constant__ WgPlan plan, const _
   if (e < M * Ntot) {
     const int row = e / Ntot, c = e - row * Ntot;
     const int xs = c >> 6, cc = c & 63;
-    if (row >= u.out_rows || cc >= u.x_valid[xs]) return;
+    const int wr = row - u.row0;
+    if (wr < 0 || wr >= u.out_rows || cc >= u.x_valid[xs]) return;
     float s = 0.0f;
     for (int p = p0; p < p1; ++p) s += a.part_w[(size_t)p * kPartFloats + e];
-    grad[u.w_off + (long long)row * u.ld + u.x_col0[xs] + cc] += s * inv;
+    grad[u.w_off + (long long)wr * u.ld + u.x_col0[xs] + cc] += s * inv;
   } else if (e < M * Ntot + 256) {
-    const int j = e - M * Ntot;
-    if (u.b_off < 0 || j >= u.out_rows) return;
+    const int j = e - M * Ntot, wr = j - u.row0;
+    if (u.b_off < 0 || wr < 0 || wr >= u.out_rows) return;
     float s = 0.0f;
     for (int p = p0; p < p1; ++p) s += a.part_b[(size_t)p * 256 + j];
-    grad[u.b_off + j] += s * inv;
-  }
-}
-
-// ------------------------------------------------------------------------------------ heads (N_out <= 4), SIMT fp32
-struct HeadArgs {
-  HeadSeg h[2];
-  int n_heads, rec_blocks;
-  const unsigned char* xrec;
-  const float* d_raw;
-  long long n_points, n_tiles;
-  float* grad;
-};
-
-__global__ void __launch_bounds__(256) head_grad_kernel(const __grid_constant__ HeadArgs a) {
-  __shared__ float4 dr[kTileM];
-  const int total_cols = a.h[0].n_cols + (a.n_heads > 1 ? a.h[1].n_cols : 0);
-  float acc[2][4];
-#pragma unroll
-  for (int i = 0; i < 2; ++i)
-#pragma unroll
-    for (int c = 0; c < 4; ++c) acc[i][c] = 0.0f;
-  float bsum = 0.0f;  // warp 0: lanes 0..3 end up with the channel sums
-  for (long long tile = blockIdx.x; tile < a.n_tiles; tile += gridDim.x) {
-    __syncthreads();
-    if (threadIdx.x < kTileM) {
-      const long long p = tile * kTileM + threadIdx.x;
-      dr[threadIdx.x] = p < a.n_points ? reinterpret_cast<const float4*>(a.d_raw)[p] : make_float4(0.f, 0.f, 0.f, 0.f);
-    }
-    __syncthreads();
-    const unsigned char* xt = a.xrec + (size_t)tile * a.rec_blocks * kBlockBytes;
-#pragma unroll
-    for (int i = 0; i < 2; ++i) {
-      const int col = threadIdx.x + i * 256;
-      if (col >= total_cols) break;
-      const int hi = col < a.h[0].n_cols ? 0 : 1;
-      const HeadSeg& hs = a.h[hi];
-      const int c = col - (hi ? a.h[0].n_cols : 0);
-      const unsigned char* base = xt + (size_t)(hs.x_blk + (c >> 6)) * kBlockBytes + (c & 7) * 2;
-      const int chunk = (c & 63) >> 3;
-      for (int r = 0; r < kTileM; ++r) {
-        const float x = __half2float(*reinterpret_cast<const __half*>(base + r * 128 + ((chunk ^ (r & 7)) << 4)));
-        const float4 d = dr[r];
-        const float dv[4] = {d.x, d.y, d.z, d.w};
-#pragma unroll
-        for (int ch = 0; ch < 4; ++ch)
-          if (ch < hs.n_ch) acc[i][ch] += dv[hs.ch0 + ch > 3 ? 3 : hs.ch0 + ch] * x;
-      }
-    }
-    if (threadIdx.x < 32) {
-      float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
-      for (int r = threadIdx.x; r < kTileM; r += 32) {
-        const float4 d = dr[r];
-        s.x += d.x; s.y += d.y; s.z += d.z; s.w += d.w;
-      }
-      s.x = warp_sum(s.x); s.y = warp_sum(s.y); s.z = warp_sum(s.z); s.w = warp_sum(s.w);
-      const int l = threadIdx.x;
-      bsum += l == 0 ? s.x : l == 1 ? s.y : l == 2 ? s.z : l == 3 ? s.w : 0.0f;
-    }
-  }
-#pragma unroll
-  for (int i = 0; i < 2; ++i) {
-    const int col = threadIdx.x + i * 256;
-    if (col >= total_cols) break;
-    const int hi = col < a.h[0].n_cols ? 0 : 1;
-    const HeadSeg& hs = a.h[hi];
-    const int c = col - (hi ? a.h[0].n_cols : 0);
-    for (int ch = 0; ch < hs.n_ch; ++ch) atomicAdd(a.grad + hs.w_off + (long long)ch * hs.n_cols + c, acc[i][ch]);
-  }
-  if (threadIdx.x < 4) {
-    for (int hi = 0; hi < a.n_heads; ++hi) {
-      const HeadSeg& hs = a.h[hi];
-      const int ch = (int)threadIdx.x - hs.ch0;
-      if (ch >= 0 && ch < hs.n_ch) atomicAdd(a.grad + hs.b_off + ch, bsum);
-    }
+    grad[u.b_off + wr] += s * inv;
   }
 }
 
@@ -572,7 +514,6 @@ bool bw_build_plan(const Graph& g, PackedBf16* p, std::vector<PackSegT>& segs, c
   WgPlan& wg = p->wg;
   memset(&bw, 0, sizeof(bw));
   memset(&wg, 0, sizeof(wg));
-  p->n_heads = 0;
   *why = nullptr;
   const int D = g.depth, wb = g.width / 64;
   size_t woff = 0;
@@ -621,12 +562,30 @@ bool bw_build_plan(const Graph& g, PackedBf16* p, std::vector<PackSegT>& segs, c
     for (int v : xcol0) u.x_col0[i++] = v;
     i = 0;
     for (int v : xvalid) u.x_valid[i++] = v;
+    u.row0 = 0;
     u.out_rows = l.out;
     u.w_off = l.w_off;
     u.ld = l.in;
     u.b_off = bias ? l.b_off : -1;
-    u.cost = u.m_blocks * u.n_x;
+    u.cost = u.m_load + u.n_x;  // the kernel is HBM-bound: cost = half-blocks loaded per stage
     return (u.m_blocks / 2) * 64 * u.n_x <= 512;
+  };
+  // head layer (N_out <= 4): dZ = channels [ch0, ch0 + l.out) of the d_raw tile, X = n_xb blocks from x_blk0
+  auto add_head = [&](const Lin& l, int ch0, int x_blk0, int n_xb) -> bool {
+    if (wg.n_units >= kMaxUnits || n_xb > kMaxXSrc) return false;
+    WgUnit& u = wg.u[wg.n_units++];
+    u.dz_blk = bw.draw_blk;
+    u.m_load = 1;
+    u.m_blocks = 2;
+    u.n_x = n_xb;
+    for (int j = 0; j < n_xb; ++j) { u.x_blk[j] = x_blk0 + j; u.x_col0[j] = 64 * j; u.x_valid[j] = 64; }
+    u.row0 = ch0;
+    u.out_rows = l.out;
+    u.w_off = l.w_off;
+    u.ld = l.in;
+    u.b_off = l.b_off;
+    u.cost = u.m_load + u.n_x;
+    return true;
   };
   if (D + 3 > kMaxStages) { *why = "too many layers"; return false; }
   if (wb != 2 && wb != 4) { *why = "width must be 128 or 256"; return false; }
@@ -653,16 +612,11 @@ bool bw_build_plan(const Graph& g, PackedBf16* p, std::vector<PackSegT>& segs, c
     for (int j = 0; j < fb; ++j) add_kb(s2, j, 4, lf, 0, 64 * j, 64, 0);
     add_kb(s2, SRC_DRAW, 1, la, 0, 0, 1, 3);
     dz_trunk[D - 1] = s2.drec_blk;
-    p->heads[0] = HeadSeg{dirh_blk, g.dir_width, 0, 3, lr.w_off, lr.b_off};
-    p->heads[1] = HeadSeg{h_blk(D - 1), g.width, 3, 1, la.w_off, la.b_off};
-    p->n_heads = 2;
   } else {
     const Lin& lo = g.lins[g.out4];
     BwStage& s0 = begin(g.width, maskL);
     add_kb(s0, SRC_DRAW, 1, lo, 0, 0, 4, 0);
     dz_trunk[D - 1] = s0.drec_blk;
-    p->heads[0] = HeadSeg{h_blk(D - 1), g.width, 0, 4, lo.w_off, lo.b_off};
-    p->n_heads = 1;
   }
   for (int i = D - 1; i >= 1; --i) {
     const Lin& l = g.lins[g.trunk[i]];
@@ -674,14 +628,18 @@ bool bw_build_plan(const Graph& g, PackedBf16* p, std::vector<PackSegT>& segs, c
   for (int s = 0; s < bw.n_stages; ++s)
     if (bw.st[s].n_kb > kMaxKB) { *why = "too many K blocks"; return false; }
   bw.ring_stage_bytes = (int)round_up(ring_max, 1024);
+  bw.draw_blk = bw.drec_blocks++;
   p->wt_bytes = woff;
 
   // ---- wgrad units
   bool ok = true;
+  if (!g.use_viewdirs) ok = ok && add_head(g.lins[g.out4], 0, h_blk(D - 1), wb);
   if (g.use_viewdirs) {
     const Lin& lf = g.lins[g.feat];
     const Lin& ld = g.lins[g.dir];
     const int feat_blk = fp.st[D].rec_blk;
+    ok = ok && add_head(g.lins[g.rgb], 0, fp.st[D + 1].rec_blk, g.dir_width / 64);
+    ok = ok && add_head(g.lins[g.alpha], 3, h_blk(D - 1), wb);
     // dir layer: X = [feat | dir encoding]
     {
       if (wg.n_units >= kMaxUnits) ok = false;
@@ -694,7 +652,7 @@ bool bw_build_plan(const Graph& g, PackedBf16* p, std::vector<PackSegT>& segs, c
         u.x_blk[u.n_x] = feat_blk + j; u.x_col0[u.n_x] = 64 * j; u.x_valid[u.n_x] = 64; u.n_x++;
       }
       if (g.Cd > 0) { u.x_blk[u.n_x] = 1; u.x_col0[u.n_x] = g.feat_width; u.x_valid[u.n_x] = g.Cd; u.n_x++; }
-      u.out_rows = ld.out; u.w_off = ld.w_off; u.ld = ld.in; u.b_off = ld.b_off; u.cost = u.m_blocks * u.n_x;
+      u.row0 = 0; u.out_rows = ld.out; u.w_off = ld.w_off; u.ld = ld.in; u.b_off = ld.b_off; u.cost = u.m_load + u.n_x;
       if (u.m_load > 2 || u.n_x > kMaxXSrc || 64 * u.n_x > 512) ok = false;
     }
     // feat / bottleneck: X = h_last
@@ -726,7 +684,7 @@ static size_t bw_smem_bytes(const BwPlan& bw, int n_g_blocks) {
   b += (2 * kRing + 2 * kMaskRing + 1 + 4 + 2) * sizeof(uint64_t) + 16;
   return b;
 }
-static size_t wg_smem_bytes() { return 1024 + (size_t)kWgStages * 8 * kHalfBytes + (2 * kWgStages + 1) * 8 + 16; }
+static size_t wg_smem_bytes() { return 1024 + (size_t)216 * 1024 + (2 * kWgMaxStages + 1) * 8 + 16; }
 
 // ------------------------------------------------------------------------------------ host: setup / workspace / launch
 void bw_free(PackedBf16* p) {
@@ -870,22 +828,15 @@ int tc_backward(const nb_model* m, int64_t n_points, float* d_raw, void* ws, siz
   wa.rec_blocks = p->plan.rec_blocks;
   wa.drec_blocks = p->bw.drec_blocks;
   wg_assign(p->wg, L.n_tiles, sm_count(), wa.part0);
+  {
+    static const int dbg = getenv("NB_WG_DEBUG") ? atoi(getenv("NB_WG_DEBUG")) : 0;
+    wa.dbg = dbg;
+  }
   const int wgrid = wa.part0[p->wg.n_units];
   mlp_tc_wgrad_kernel<<<wgrid, kThreadsWg, wg_smem_bytes(), stream>>>(p->wg, wa);
   NB_LAUNCHED();
   dim3 rgrid((unsigned)ceil_div(kPartFloats + 256, 256), (unsigned)p->wg.n_units);
   wgrad_reduce_kernel<<<rgrid, 256, 0, stream>>>(p->wg, wa, absmax, grad);
-  NB_LAUNCHED();
-  HeadArgs ha{};
-  for (int i = 0; i < p->n_heads; ++i) ha.h[i] = p->heads[i];
-  ha.n_heads = p->n_heads;
-  ha.rec_blocks = p->plan.rec_blocks;
-  ha.xrec = ba.xrec;
-  ha.d_raw = d_raw;
-  ha.n_points = n_points;
-  ha.n_tiles = L.n_tiles;
-  ha.grad = grad;
-  head_grad_kernel<<<(int)std::min<int64_t>(L.n_tiles, 2 * sm_count()), 256, 0, stream>>>(ha);
   NB_LAUNCHED();
   return NB_OK;
 }

@@ -53,11 +53,12 @@ struct BwStage {
 };
 struct BwPlan {
   int n_stages, drec_blocks, ring_stage_bytes;
+  int draw_blk;         // dZ-record block of the scaled 16-bit d_raw tile (operand of the head wgrad units)
   BwStage st[kMaxStages];
 };
 
 // ---- wgrad work: unit = one (dZ, X) pair of record block ranges -> one weight sub-matrix
-constexpr int kMaxUnits = 16;
+constexpr int kMaxUnits = 20;
 constexpr int kMaxXSrc = 6;
 struct WgUnit {
   int dz_blk;        // first dZ-record block
@@ -67,6 +68,7 @@ struct WgUnit {
   int x_blk[kMaxXSrc];     // X-record block of each
   int x_col0[kMaxXSrc];    // destination column of each block's element 0 in the weight matrix
   int x_valid[kMaxXSrc];   // valid columns of each block (<= 64)
+  int row0;          // accumulator rows [row0, row0 + out_rows) are weight rows [0, out_rows)
   int out_rows;      // valid rows (layer out)
   long long w_off;   // float offset of weight[0,0]
   int ld;            // weight leading dimension (layer in)
@@ -96,13 +98,6 @@ struct BiasSeg {
   int dst, count;
   long long src_off;
 };
-// SIMT head gradients (rgb / alpha / out4 layers: N_out <= 4)
-struct HeadSeg {
-  int x_blk, n_cols;      // X-record block range start, columns (multiple of 64)
-  int ch0, n_ch;          // d_raw channels [ch0, ch0+n_ch)
-  long long w_off, b_off; // weight [n_ch, n_cols] row-major, bias [n_ch]
-};
-
 struct PackedBf16 {
   TcPlan plan;
   unsigned char* d_w = nullptr;
@@ -116,8 +111,6 @@ struct PackedBf16 {
   // backward
   BwPlan bw;
   WgPlan wg;
-  HeadSeg heads[2];
-  int n_heads = 0;
   unsigned char* d_wt = nullptr;  // transposed images for the dgrad chain
   PackSegT* d_segs_t = nullptr;
   int n_segs_t = 0;
