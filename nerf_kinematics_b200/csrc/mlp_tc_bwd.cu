@@ -319,7 +319,7 @@ struct WgArgs {
   const unsigned char* xrec;
   const unsigned char* drec;
   float* part_w;   // [grid][65536]
-  float* part_b;   // [grid][256]
+  float* part_b;   // [grid][4 row groups][256]
   long long n_tiles;
   int rec_blocks, drec_blocks;
   int part0[kMaxUnits + 1];  // CTA b works on unit u with part0[u] <= b < part0[u+1]
@@ -421,30 +421,41 @@ mlp_tc_wgrad_kernel(const __grid_constant__ WgPlan plan, const __grid_constant__
       tc_commit(smem_u32(bar_done));
     }
   } else {
-    // ---- bias gradient: column sums of the dZ tiles while they sit in shared memory
+    // ---- bias gradient: column sums of the dZ tiles while they sit in shared memory.  Warp w sums rows
+    // [16w, 16w+16) of every stage; lane l owns the 16-byte chunk l of the 256-column row (block l>>3, chunk l&7).
     const int t = threadIdx.x - 64;
-    const int blk = t >> 5, chunk = (t & 31) >> 2, within = (t & 3) * 4;
+    const int rg = t >> 5, blk = lane >> 3, chunk = lane & 7;
     const bool active = u.b_off >= 0 && blk < u.m_load && !(a.dbg & 4);
-    float s0 = 0.0f, s1 = 0.0f;
+    float cs[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) cs[i] = 0.0f;
     uint32_t slot = 0, phase = 0;
     for (long long it = 0; it < n_steps; ++it) {
       mbar_wait(smem_u32(bar_full + slot), phase);
       if (active) {
-        const unsigned char* base = stages + slot * stage_bytes + blk * kHalfBytes + within;
-#pragma unroll 8
-        for (int r = 0; r < 64; ++r) {
-          const __half2 h = *reinterpret_cast<const __half2*>(base + r * 128 + ((chunk ^ (r & 7)) << 4));
-          const float2 f = __half22float2(h);
-          s0 += f.x;
-          s1 += f.y;
+        const uint32_t base = smem_u32(stages + slot * stage_bytes + blk * kHalfBytes + rg * 16 * 128);
+#pragma unroll
+        for (int r = 0; r < 16; ++r) {
+          uint4 v;
+          asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];"
+                       : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w)
+                       : "r"(base + r * 128 + ((chunk ^ (r & 7)) << 4)));
+          const float2 f0 = __half22float2(*reinterpret_cast<const __half2*>(&v.x));
+          const float2 f1 = __half22float2(*reinterpret_cast<const __half2*>(&v.y));
+          const float2 f2 = __half22float2(*reinterpret_cast<const __half2*>(&v.z));
+          const float2 f3 = __half22float2(*reinterpret_cast<const __half2*>(&v.w));
+          cs[0] += f0.x; cs[1] += f0.y; cs[2] += f1.x; cs[3] += f1.y;
+          cs[4] += f2.x; cs[5] += f2.y; cs[6] += f3.x; cs[7] += f3.y;
         }
       }
       mbar_arrive(smem_u32(bar_empty + slot));
       if (++slot == kWgStages) { slot = 0; phase ^= 1; }
     }
-    float* pb = a.part_b + (size_t)blockIdx.x * 256;
-    pb[2 * t] = s0;
-    pb[2 * t + 1] = s1;
+    {
+      float4* pb = reinterpret_cast<float4*>(a.part_b + ((size_t)blockIdx.x * 4 + rg) * 256 + lane * 8);
+      pb[0] = make_float4(cs[0], cs[1], cs[2], cs[3]);
+      pb[1] = make_float4(cs[4], cs[5], cs[6], cs[7]);
+    }
     // ---- accumulators -> partial buffer
     mbar_wait(smem_u32(bar_done), 0);
     tc_fence_after();
@@ -498,7 +509,7 @@ __global__ void wgrad_reduce_kernel(const __grid_constant__ WgPlan plan, const _
     const int j = e - M * Ntot, wr = j - u.row0;
     if (u.b_off < 0 || wr < 0 || wr >= u.out_rows) return;
     float s = 0.0f;
-    for (int p = p0; p < p1; ++p) s += a.part_b[(size_t)p * 256 + j];
+    for (int p = 4 * p0; p < 4 * p1; ++p) s += a.part_b[(size_t)p * 256 + j];
     grad[u.b_off + wr] += s * inv;
   }
 }
@@ -739,7 +750,7 @@ static BwLayout bw_layout(const PackedBf16* p, int64_t n_points) {
   L.off_xrec = take((size_t)L.n_tiles * p->plan.rec_blocks * kBlockBytes);
   L.off_drec = take((size_t)L.n_tiles * p->bw.drec_blocks * kBlockBytes);
   L.off_pw = take((size_t)L.max_ctas * kPartFloats * sizeof(float));
-  L.off_pb = take((size_t)L.max_ctas * 256 * sizeof(float));
+  L.off_pb = take((size_t)L.max_ctas * 4 * 256 * sizeof(float));
   L.total = off;
   return L;
 }
