@@ -210,7 +210,8 @@ def run_ours(args):
     if prec_name == "auto":
         prec_name = "bf16" if getattr(nk, "BF16_BACKWARD", False) else "fp32"
     step = TrainStep(mc, mf, N_samples=N_SAMPLES, N_importance=N_IMPORTANCE, perturb=1.0, raw_noise_std=0.0,
-                     white_bkgd=True, precision=prec_name, lrate=5e-4, lrate_decay=500, world_size=world)
+                     white_bkgd=True, precision=prec_name, lrate=5e-4, lrate_decay=500, world_size=world,
+                     cuda_graph=not args.no_graph)
     # ---- synthetic inputs of the named shape: one 800x800 pose, N_rand rays per step without replacement
     c2w = torch.from_numpy(pose_spherical(30.0 + 7.0 * rank, -30.0, 4.0))
     ro, rd = nk.get_rays(H, W, FOCAL, c2w)
@@ -246,6 +247,7 @@ def run_ours(args):
             fn(i)
         barrier()
         ops.launch_count_reset()
+        replays0 = step.graph_replays
         sampler = ClockSampler(torch.cuda.current_device() if "CUDA_VISIBLE_DEVICES" not in os.environ else
                                os.environ["CUDA_VISIBLE_DEVICES"].split(",")[local])
         sampler.start()
@@ -259,7 +261,9 @@ def run_ours(args):
         t = torch.tensor([e0.elapsed_time(e1) * 1e-3], device=dev)
         if world > 1:
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        return float(t), ops.launch_count(), clocks, last
+        # kernels inside a replayed CUDA graph are counted once at capture: add them per replay
+        launches = ops.launch_count() + (step.launches_per_step or 0) * (step.graph_replays - replays0)
+        return float(t), launches, clocks, last
 
     t_res, launches, clocks, last_loss = timed(resident_step)
     t_e2e, _, _, _ = timed(e2e_step)
@@ -280,7 +284,8 @@ def run_ours(args):
             "steps": K, "warmup": Wm, "ms_per_step": 1e3 * t_res / K, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "bf16" if prec_name == "bf16" else "f32", "data": "synthetic",
             "config": {"workload": WORKLOAD, "rays_per_step_per_gpu": N_RAND, "n_samples": N_SAMPLES,
-                       "n_importance": N_IMPORTANCE, "mlp_precision": prec_name, "optimizer": "Adam (in the timed region)",
+                       "n_importance": N_IMPORTANCE, "mlp_precision": prec_name, "optimizer": "fused Adam (in the timed region)",
+                       "cuda_graph": bool(step.use_graph),
                        "l2": "per-step working set (saved activations of 262144 points) exceeds the 126 MB L2; "
                              "a different ray batch every step"},
             "e2e": {"value": e2e, "unit": "rays/s", "h2d_bytes_per_step": N_RAND * 9 * 4 * world,
@@ -308,6 +313,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--precision", default="auto", choices=["auto", "bf16", "fp32"])
+    ap.add_argument("--no-graph", action="store_true", help="launch the train step kernel by kernel (no CUDA graph)")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)

@@ -240,6 +240,17 @@ int nb_render_rays_backward(const nb_model_t* coarse, const nb_model_t* fine, co
 int nb_mse_loss(const float* pred, const float* target, int64_t count, float grad_scale, float* loss_out,
                 float* d_pred, nb_stream_t stream);
 
+/* ---------------------------------------------------------------- a13 optimizer step
+ * Adam over a flat fp32 parameter buffer, one launch, gradients consumed and zeroed for the next step.
+ * Replaces optimizer.step() + zero_grad() (PT train_nerf.py:288-289, torch.optim.Adam: denom = sqrt(v)/sqrt(bc2)+eps,
+ * p -= lr/bc1 * m/denom) or, with tf_style != 0, tf.train.AdamOptimizer.apply_gradients (TF run_nerf.py:827:
+ * lr_t = lr*sqrt(bc2)/bc1, p -= lr_t*m/(sqrt(v)+eps)).
+ * hyper is a DEVICE array of 8 floats {lr, beta1, beta2, eps, bc1 = 1-beta1^t, bc2 = 1-beta2^t, 1-beta1, 1-beta2}
+ * (each formed in double precision on the host, like the frameworks do), so that a captured
+ * CUDA graph of the whole train step sees the new learning rate / step count on every replay. */
+int nb_adam_step(float* params, float* grads, float* exp_avg, float* exp_avg_sq, int64_t n, const float* hyper,
+                 int tf_style, int zero_grads, nb_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -26,6 +26,7 @@ SOURCES = [
     ("mlp_tc.cu", []),
     ("mlp_tc_bwd.cu", []),
     ("render.cu", ["--fmad=false"]),
+    ("optim.cu", ["--fmad=false"]),
 ]
 
 

@@ -71,6 +71,7 @@ SIGNATURES = {
     "nb_sample_fine": (i32, [p, p, i64, i32, p, i32, p, p, p, p]),
     "nb_merge_sorted": (i32, [p, i32, p, i32, i64, p, p]),
     "nb_mse_loss": (i32, [p, p, i64, f32, p, p, p]),
+    "nb_adam_step": (i32, [p, p, p, p, i64, p, i32, i32, p]),
     "nb_render_workspace_bytes": (sz, [p, p, i32, i64, C.POINTER(RenderCfg)]),
     "nb_render_rays": (i32, [p, p, p, i32, i64, C.POINTER(RenderCfg), C.POINTER(RenderRand), C.POINTER(RenderOut), p,
                              sz, p]),

@@ -139,13 +139,18 @@ class KernelMLP(nn.Module):
     def _fingerprint(self):
         return tuple(p._version for p in self.parameters()) + (self._flat.data_ptr(),)
 
-    def prepare(self, precision=None):
-        """Make the native handle current for `precision`; returns (handle, precision id)."""
+    def mark_params_changed(self):
+        """The flat buffer was written by a kernel (fused Adam): torch's version counters did not see it."""
+        self._packed_fp = {}
+
+    def prepare(self, precision=None, force=False):
+        """Make the native handle current for `precision`; returns (handle, precision id).  `force` repacks the
+        16-bit images unconditionally (the captured train step must not depend on host-side version checks)."""
         prec = precision_id(self.precision if precision is None else precision)
         self.flatten_parameters()
         if prec == 1:
             fp = self._fingerprint()
-            if self._packed_fp.get(prec) != fp:
+            if force or self._packed_fp.get(prec) != fp:
                 with torch.cuda.device(self._flat.device):
                     check(lib().nb_model_pack(self._handle, prec,
                                               C.c_void_p(torch.cuda.current_stream().cuda_stream)), "nb_model_pack")

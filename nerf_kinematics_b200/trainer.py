@@ -6,8 +6,17 @@ fine networks, loss = mse(rgb_fine, tgt) + mse(rgb_coarse, tgt), backward, [all-
 exponential learning-rate decay.  Unlike `loss.backward()` through render() (which also works), it
 drives nb_render_rays / nb_mse_loss / nb_render_rays_backward directly into ONE flat fp32 gradient
 bucket holding both networks, which is what the data-parallel all-reduce (NCCL over NVLink) sends.
+
+Two B200-side additions over the reference loop, both optional:
+  * fused Adam (nb_adam_step): one launch per network instead of torch's ~7 multi-tensor launches; the moments live
+    in flat buffers that a regular torch.optim.Adam object aliases, so `optimizer.state_dict()` keeps the reference's
+    checkpoint layout (train_nerf.py:401-414);
+  * CUDA graph: the whole device side of an iteration (weight repack, render, loss, backward, all-reduce, Adam) is
+    captured once per batch shape and replayed with one launch; learning rate and bias corrections are read from a
+    small device array refreshed before each replay.
 """
 import ctypes as C
+import math
 
 import torch
 
@@ -18,25 +27,35 @@ from .ops import _f32, _optptr, _stream
 from .render_core import OUT_KEYS, _random_inputs
 
 
+def _round_up(a, b):
+    return (a + b - 1) // b * b
+
+
 class TrainStep:
     def __init__(self, model_coarse, model_fine, *, N_samples=64, N_importance=128, perturb=1.0, raw_noise_std=0.0,
                  white_bkgd=False, lindisp=False, precision=None, lrate=5e-4, lrate_decay=250, decay_rate=0.1,
-                 eps=1e-8, process_group=None, world_size=1, optimizer=None):
+                 eps=1e-8, betas=(0.9, 0.999), process_group=None, world_size=1, optimizer=None, fused_adam=None,
+                 tf_adam=False, cuda_graph=False):
         self.mc, self.mf = model_coarse, (model_fine if N_importance > 0 else None)
         self.S, self.I = int(N_samples), int(N_importance)
         self.perturb, self.noise, self.white, self.lindisp = perturb, raw_noise_std, white_bkgd, lindisp
         self.prec = precision_id(model_coarse.precision if precision is None else precision)
         self.lrate, self.decay_steps, self.decay_rate = lrate, lrate_decay * 1000, decay_rate
+        self.betas, self.eps, self.tf_adam = tuple(betas), float(eps), bool(tf_adam)
         self.pg, self.world = process_group, int(world_size)
+        self.fused = (optimizer is None) if fused_adam is None else bool(fused_adam)
+        self.use_graph = bool(cuda_graph) and self.fused
         self.mc.flatten_parameters()
         nc = self.mc.n_params
         nf = self.mf.n_params if self.mf is not None else 0
         dev = self.mc._flat.device
+        self.dev = dev
         if self.mf is not None:
             self.mf.flatten_parameters()
-        # one bucket for both networks: [coarse | fine]
-        self.bucket = torch.zeros((nc + nf,), dtype=torch.float32, device=dev)
-        self.gc, self.gf = self.bucket[:nc], (self.bucket[nc:] if nf else None)
+        # one bucket for both networks: [coarse | pad | fine]; the fine part starts 256-byte aligned
+        off_f = _round_up(nc, 64)
+        self.bucket = torch.zeros((off_f + nf,), dtype=torch.float32, device=dev)
+        self.gc, self.gf = self.bucket[:nc], (self.bucket[off_f:off_f + nf] if nf else None)
         params = []
         for m, gflat in ((self.mc, self.gc), (self.mf, self.gf)):
             if m is None:
@@ -45,29 +64,83 @@ class TrainStep:
                 p.grad = gv
                 params.append(p)
         self.params = params
-        self.opt = optimizer if optimizer is not None else torch.optim.Adam(params, lr=lrate, betas=(0.9, 0.999), eps=eps)
+        self.opt = optimizer if optimizer is not None else torch.optim.Adam(params, lr=lrate, betas=self.betas, eps=eps)
         self.global_step = 0
         self.loss_buf = torch.zeros((2,), dtype=torch.float32, device=dev)
         self._ws = None
-        self._ws_key = None
+        self._ws_cache = {}
+        self._graphs = {}
+        self.launches_per_step = None  # kernels inside one captured iteration (graph mode)
+        self.graph_replays = 0
+        if self.fused:
+            # Adam moments in the bucket's layout; the torch optimizer's per-parameter state aliases them
+            self.exp_avg = torch.zeros_like(self.bucket)
+            self.exp_avg_sq = torch.zeros_like(self.bucket)
+            self._segments = [(self.mc, 0, nc)] + ([(self.mf, off_f, nf)] if nf else [])
+            self._step_t = torch.zeros((), dtype=torch.float32)  # torch keeps `step` as a CPU fp32 scalar tensor
+            self._alias_optimizer_state()
+            self.hyper_host = torch.zeros((8,), dtype=torch.float32).pin_memory() if dev.type == "cuda" else None
+            self.hyper = torch.zeros((8,), dtype=torch.float32, device=dev)
 
+    # ------------------------------------------------------------------ optimizer state (checkpoint layout)
+    def _alias_optimizer_state(self):
+        for m, off, _ in self._segments:
+            for (p, _gv), (_p2, mv), (_p3, vv) in zip(m.grad_views(self.bucket[off:off + m.n_params]),
+                                                      m.grad_views(self.exp_avg[off:off + m.n_params]),
+                                                      m.grad_views(self.exp_avg_sq[off:off + m.n_params])):
+                self.opt.state[p] = {"step": self._step_t, "exp_avg": mv, "exp_avg_sq": vv}
+
+    def optimizer_state_dict(self):
+        """torch.optim.Adam-format state (the reference checkpoint's `optimizer_state_dict`, train_nerf.py:408)."""
+        if self.fused:
+            self._step_t.fill_(float(self.global_step))
+        return self.opt.state_dict()
+
+    def load_optimizer_state_dict(self, sd):
+        """Resume from a reference checkpoint's optimizer state (train_nerf.py:184-190)."""
+        self.opt.load_state_dict(sd)
+        if not self.fused:
+            return
+        step = 0
+        for m, off, _ in self._segments:
+            for (p, _g), (_p2, mv), (_p3, vv) in zip(m.grad_views(self.bucket[off:off + m.n_params]),
+                                                     m.grad_views(self.exp_avg[off:off + m.n_params]),
+                                                     m.grad_views(self.exp_avg_sq[off:off + m.n_params])):
+                st = self.opt.state.get(p)
+                if st:
+                    mv.copy_(st["exp_avg"])
+                    vv.copy_(st["exp_avg_sq"])
+                    step = max(step, int(float(st["step"])))
+        self.global_step = step
+        self._alias_optimizer_state()
+
+    def learning_rate(self, step_index):
+        """lr used by iteration `step_index` (0-based): lr0 * decay_rate ** (i / decay_steps) (run_nerf.py:705-709,
+        train_nerf.py:292-297 set it after iteration i-1 for iteration i)."""
+        return self.lrate * (self.decay_rate ** (step_index / self.decay_steps))
+
+    # ------------------------------------------------------------------ device side of one iteration
     def _workspace(self, n, stride, cfg, hc, hf, dev):
+        """Workspace and output buffers per batch shape (kept alive: captured graphs hold their addresses)."""
         key = (n, stride)
-        if self._ws_key != key:
+        ent = self._ws_cache.get(key)
+        if ent is None:
             nbytes = lib().nb_render_workspace_bytes(hc, hf, stride, n, C.byref(cfg))
-            self._ws = torch.empty((max(int(nbytes), 1),), dtype=torch.uint8, device=dev)
-            self._ws_key = key
             f = lambda *s: torch.empty(s, dtype=torch.float32, device=dev)
-            self._out = {"rgb": f(n, 3), "rgb0": f(n, 3)}
-            self._d = {"rgb": f(n, 3), "rgb0": f(n, 3)}
+            ent = (torch.empty((max(int(nbytes), 1),), dtype=torch.uint8, device=dev),
+                   {"rgb": f(n, 3), "rgb0": f(n, 3)}, {"rgb": f(n, 3), "rgb0": f(n, 3)})
+            if len(self._ws_cache) >= 4 and not self._graphs:
+                self._ws_cache.clear()
+            self._ws_cache[key] = ent
+        self._ws, self._out, self._d = ent
         return self._ws
 
-    def forward_backward(self, rays, target, rnd=None):
+    def forward_backward(self, rays, target, rnd=None, force_pack=False, zero_bucket=True):
         """Render + loss + backward into the flat bucket.  Returns the (device) loss tensor [2] = (fine, coarse)."""
         rays, target = _f32(rays, "rays"), _f32(target, "target")
         n, stride, dev = rays.shape[0], rays.shape[1], rays.device
-        hc, _ = self.mc.prepare(self.prec)
-        hf = self.mf.prepare(self.prec)[0] if self.mf is not None else None
+        hc, _ = self.mc.prepare(self.prec, force=force_pack)
+        hf = self.mf.prepare(self.prec, force=force_pack)[0] if self.mf is not None else None
         cfg = RenderCfg(self.S, self.I, int(self.lindisp), int(self.white), self.prec, 1)
         ws = self._workspace(n, stride, cfg, hc, hf, dev)
         rnd = _random_inputs(n, self.S, self.I, dev, self.perturb, self.noise, rnd)
@@ -84,7 +157,8 @@ class TrainStep:
             check(lib().nb_render_rays(hc, hf, C.c_void_p(rays.data_ptr()), stride, n, C.byref(cfg), C.byref(rs),
                                        C.byref(o), C.c_void_p(ws.data_ptr()), ws.numel(), st), "nb_render_rays")
             self.loss_buf.zero_()
-            self.bucket.zero_()
+            if zero_bucket:
+                self.bucket.zero_()
             check(lib().nb_mse_loss(C.c_void_p(out["rgb"].data_ptr()), C.c_void_p(target.data_ptr()), n * 3, scale,
                                     C.c_void_p(self.loss_buf.data_ptr()), C.c_void_p(self._d["rgb"].data_ptr()), st))
             gk = {"d_rgb": self._d["rgb"]}
@@ -106,11 +180,84 @@ class TrainStep:
             import torch.distributed as dist
             dist.all_reduce(self.bucket, op=dist.ReduceOp.SUM, group=self.pg)
 
+    def _fused_adam(self):
+        """nb_adam_step per network; gradients are cleared by the same pass (the next backward accumulates)."""
+        with torch.cuda.device(self.dev):
+            st = _stream()
+            for m, off, cnt in self._segments:
+                check(lib().nb_adam_step(C.c_void_p(m._flat.data_ptr()), C.c_void_p(self.bucket.data_ptr() + 4 * off),
+                                         C.c_void_p(self.exp_avg.data_ptr() + 4 * off),
+                                         C.c_void_p(self.exp_avg_sq.data_ptr() + 4 * off), cnt,
+                                         C.c_void_p(self.hyper.data_ptr()), int(self.tf_adam), 1, st), "nb_adam_step")
+                m.mark_params_changed()
+
+    def _device_iteration(self, rays, target, rnd=None):
+        """Everything of one iteration that runs on the GPU, in stream order (capturable in a CUDA graph)."""
+        loss = self.forward_backward(rays, target, rnd, force_pack=True, zero_bucket=False)
+        self.allreduce()
+        self._fused_adam()
+        return loss
+
+    def _set_hyper(self):
+        """lr and bias corrections of the iteration about to run -> device (read by nb_adam_step)."""
+        t = self.global_step + 1
+        b1, b2 = self.betas
+        vals = [self.learning_rate(self.global_step), b1, b2, self.eps, 1.0 - b1 ** t, 1.0 - b2 ** t, 1.0 - b1, 1.0 - b2]
+        if self.hyper_host is not None:
+            for i, v in enumerate(vals):
+                self.hyper_host[i] = v
+            self.hyper.copy_(self.hyper_host, non_blocking=True)
+        else:
+            self.hyper.copy_(torch.tensor(vals, dtype=torch.float32))
+
+    def _graph_for(self, rays, target):
+        key = (tuple(rays.shape), tuple(target.shape))
+        g = self._graphs.get(key)
+        if g is not None:
+            return g
+        s_rays, s_tgt = torch.empty_like(rays), torch.empty_like(target)
+        s_rays.copy_(rays)
+        s_tgt.copy_(target)
+        # one eager iteration's worth of lazy setup (library buffers, function attributes) must precede the capture:
+        # run the forward/backward once without touching parameters or moments
+        self.forward_backward(s_rays, s_tgt, force_pack=True, zero_bucket=False)
+        self.bucket.zero_()
+        torch.cuda.synchronize(self.dev)
+        graph = torch.cuda.CUDAGraph()
+        before = ops.launch_count()
+        with torch.cuda.graph(graph):
+            self._device_iteration(s_rays, s_tgt)
+        self.launches_per_step = ops.launch_count() - before
+        g = (graph, s_rays, s_tgt)
+        self._graphs[key] = g
+        return g
+
+    # ------------------------------------------------------------------ public
     def step(self, rays, target, rnd=None):
         """One full iteration; returns the device loss tensor [2] (fine, coarse) of this rank's batch."""
+        if not self.fused:
+            return self._step_torch_optimizer(rays, target, rnd)
+        self._set_hyper()
+        if self.use_graph and rnd is None:
+            rays, target = _f32(rays, "rays"), _f32(target, "target")
+            graph, s_rays, s_tgt = self._graph_for(rays, target)
+            s_rays.copy_(rays, non_blocking=True)
+            s_tgt.copy_(target, non_blocking=True)
+            graph.replay()
+            self.graph_replays += 1
+            loss = self.loss_buf
+        else:
+            loss = self._device_iteration(rays, target, rnd)
+        self.global_step += 1
+        lr = self.learning_rate(self.global_step)
+        for gparam in self.opt.param_groups:
+            gparam["lr"] = lr
+        return loss
+
+    def _step_torch_optimizer(self, rays, target, rnd=None):
+        """The reference's own optimizer object (any torch.optim) on the parameters' .grad views of the bucket."""
         loss = self.forward_backward(rays, target, rnd)
         self.allreduce()
-        # the optimizer reads p.grad, which are views of the bucket
         for m, gflat in ((self.mc, self.gc), (self.mf, self.gf)):
             if m is None:
                 continue
@@ -119,7 +266,7 @@ class TrainStep:
                     p.grad = gv
         self.opt.step()
         self.global_step += 1
-        new_lr = self.lrate * (self.decay_rate ** (self.global_step / self.decay_steps))
+        new_lr = self.learning_rate(self.global_step)
         for gparam in self.opt.param_groups:
             gparam["lr"] = new_lr
         return loss

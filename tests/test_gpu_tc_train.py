@@ -4,6 +4,7 @@ chain, split-K wgrad, head gradients -- against the fp32 kernels and the oracle'
 Reference being matched: tf.GradientTape / loss.backward() through run_network + the network
 (nerf/run_nerf.py:807-826, nerf-pytorch/train_nerf.py:286)."""
 import ctypes as C
+import math
 
 import pytest
 import torch
@@ -279,3 +280,99 @@ def test_tc_train_step_against_oracle_autograd():
         # the fine network's samples depend on the coarse weights through a discontinuous sampler: direction, not bits
         assert cos >= (0.995 if name == "coarse" else 0.97), (name, cos)
         assert 0.9 <= gn / rn <= 1.1, (name, gn, rn)
+
+
+# ------------------------------------------------------------------------------------ fused Adam + CUDA-graph step
+def _train_setup(seed=0, **kw):
+    from nerf_kinematics_b200.trainer import TrainStep
+    sdc, sdf = O.init_flexible_state(seed=seed), O.init_flexible_state(seed=seed + 1)
+    mc, mf = nk.model_from_state_dict(sdc).to(DEV), nk.model_from_state_dict(sdf).to(DEV)
+    g = load_golden("train_flexible")
+    rays, tgt = g["rays"][:64].to(DEV), g["target"][:64].to(DEV)
+    st = TrainStep(mc, mf, N_samples=64, N_importance=128, perturb=0.0, white_bkgd=True, lrate=5e-3, lrate_decay=1, **kw)
+    return st, mc, mf, rays, tgt
+
+
+@pytest.mark.parametrize("n", [4096, 1000003])
+def test_adam_kernel_matches_torch_adam(n):
+    """nb_adam_step against torch.optim.Adam (PT train_nerf.py:288-289) and the TF formula (run_nerf.py:827) on
+    identical gradients, 3 steps with changing learning rate."""
+    g = torch.Generator().manual_seed(n)
+    p0 = torch.randn(n, generator=g).to(DEV)
+    grads = [(torch.randn(n, generator=g) * 10 ** float(torch.randint(-6, 0, (1,), generator=g))).to(DEV) for _ in range(3)]
+    ref = torch.nn.Parameter(p0.clone())
+    opt = torch.optim.Adam([ref], lr=1e-3, betas=(0.9, 0.999), eps=1e-8, foreach=False)
+    for tf_style in (0, 1):
+        p, m, v = p0.clone(), torch.zeros(n, device=DEV), torch.zeros(n, device=DEV)
+        pt, mt, vt = p0.double().clone(), torch.zeros(n, device=DEV, dtype=torch.float64), torch.zeros(n, device=DEV, dtype=torch.float64)
+        for t, gr in enumerate(grads, 1):
+            lr = 1e-3 * 0.5 ** (t - 1)
+            hyper = torch.tensor([lr, 0.9, 0.999, 1e-8, 1 - 0.9 ** t, 1 - 0.999 ** t, 1 - 0.9, 1 - 0.999], dtype=torch.float32, device=DEV)
+            gbuf = gr.clone()
+            check(lib().nb_adam_step(_ptr(p), _ptr(gbuf), _ptr(m), _ptr(v), n, _ptr(hyper), tf_style, 1, _stream()))
+            assert float(gbuf.abs().max()) == 0.0  # zero_grad fused
+            if tf_style == 0:
+                opt.param_groups[0]["lr"] = lr
+                ref.grad = gr.clone()
+                opt.step()
+            else:
+                mt = 0.9 * mt + 0.1 * gr.double()
+                vt = 0.999 * vt + 0.001 * gr.double() ** 2
+                pt = pt - lr * math.sqrt(1 - 0.999 ** t) / (1 - 0.9 ** t) * mt / (vt.sqrt() + 1e-8)
+        if tf_style == 0:
+            st = opt.state[ref]
+            assert maxdiff(p, ref.detach()) <= 2e-6
+            assert maxdiff(m, st["exp_avg"]) <= 1e-6 * float(st["exp_avg"].abs().max())
+            assert maxdiff(v, st["exp_avg_sq"]) <= 1e-6 * float(st["exp_avg_sq"].abs().max())
+        else:
+            assert maxdiff(p, pt) <= 2e-6
+
+
+@pytest.mark.parametrize("prec", ["fp32", "bf16"])
+def test_fused_adam_train_step_and_checkpoint_layout(prec):
+    """TrainStep with the fused optimizer against TrainStep driving torch.optim.Adam: same loss trajectory (early Adam
+    updates are sign-like, so parameters whose gradient is ~0 may legitimately differ), same learning-rate schedule,
+    and an optimizer state dict in the reference checkpoint's layout (train_nerf.py:401-414) that round-trips."""
+    a, mca, mfa, rays, tgt = _train_setup(precision=prec, fused_adam=True)
+    b, mcb, mfb, _, _ = _train_setup(precision=prec, fused_adam=False)
+    for _ in range(4):
+        la = a.step(rays, tgt).clone()
+        lb = b.step(rays, tgt).clone()
+        assert maxdiff(la, lb) <= 2e-3
+    assert abs(a.opt.param_groups[0]["lr"] - b.opt.param_groups[0]["lr"]) < 1e-12
+    sa, sb = a.optimizer_state_dict(), b.opt.state_dict()
+    assert sa["state"].keys() == sb["state"].keys()
+    assert sa["param_groups"][0]["params"] == sb["param_groups"][0]["params"]
+    for k in sa["state"]:
+        assert float(sa["state"][k]["step"]) == float(sb["state"][k]["step"]) == 4.0
+        assert sa["state"][k]["exp_avg"].shape == sb["state"][k]["exp_avg"].shape
+    c, mcc, mfc, _, _ = _train_setup(precision=prec, fused_adam=True)
+    c.load_optimizer_state_dict(sb)
+    assert c.global_step == 4
+    k0 = next(iter(sb["state"]))
+    assert maxdiff(c.exp_avg[: sb["state"][k0]["exp_avg"].numel()].view_as(sb["state"][k0]["exp_avg"]), sb["state"][k0]["exp_avg"]) == 0.0
+
+
+def test_cuda_graph_step_equals_eager_step():
+    """The captured iteration (repack, render, loss, backward, Adam in ONE graph launch) replays to the same
+    parameters as the eager sequence; perturb=0 so both see identical samples."""
+    a, mca, mfa, rays, tgt = _train_setup(precision="bf16", cuda_graph=True)
+    b, mcb, mfb, _, _ = _train_setup(precision="bf16", cuda_graph=False)
+    losses = []
+    for i in range(5):
+        r = torch.roll(rays, i, 0)
+        t = torch.roll(tgt, i, 0)
+        la, lb = a.step(r, t).clone(), b.step(r, t).clone()
+        losses.append(float(la[0]))
+        assert maxdiff(la, lb) <= 1e-6, i
+    assert a.graph_replays == 5 and a.launches_per_step and a.launches_per_step >= 10
+    for (k, pa), (_, pb) in zip(list(mca.named_parameters()) + list(mfa.named_parameters()),
+                                list(mcb.named_parameters()) + list(mfb.named_parameters())):
+        assert maxdiff(pa, pb) <= 1e-6 + 1e-5 * float(pb.detach().abs().max()), k
+    assert losses[-1] < losses[0]
+    # rendering with the updated weights works after graph steps (the 16-bit images are repacked on demand)
+    from nerf_kinematics_b200.render_core import render_chunk
+    with torch.no_grad():
+        oa = render_chunk(rays, mca, mfa, N_samples=64, N_importance=128, white_bkgd=True, precision="bf16")
+        ob = render_chunk(rays, mcb, mfb, N_samples=64, N_importance=128, white_bkgd=True, precision="bf16")
+    assert maxdiff(oa["rgb"], ob["rgb"]) <= 1e-4
