@@ -1,28 +1,34 @@
-// Fused bf16 tensor-core MLP (NB_PREC_BF16) for sm_100a: positional encoding + every layer of the
+// Fused 16-bit tensor-core MLP (NB_PREC_BF16) for sm_100a: positional encoding + every layer of the
 // network in ONE persistent kernel; activations never leave the SM between layers.
 //
 // What it computes: run_network + the network forward (nerf/run_nerf.py:30-45 with the Embedder of
 // nerf/run_nerf_helpers.py:22-56 and the graph of :80-118; nerf-pytorch/nerf/train_utils.py:8-25 with
-// models.py:233-256) for a tile of 128 points at a time.
+// models.py:233-256) for PAIRS of 128-point tiles.
 //
 // How (Blackwell execution model):
-//   * one CTA per SM, persistent over 128-point tiles; 6 warps with fixed roles:
-//       warp 0    weight producer  -- streams pre-swizzled bf16 weight chunks (N x 64 K-elements, the exact
-//                                     UMMA SWIZZLE_128B K-major image) from L2 into a shared-memory ring with
-//                                     bulk async copies (cp.async.bulk -> UBLKCP) completing on mbarriers;
-//       warp 1    MMA issuer       -- one thread issues tcgen05.mma (kind::f16, bf16 x bf16 -> fp32, M=128,
-//                                     N<=256, K=16) with A = activations in shared memory, B = the ring,
-//                                     D = fp32 accumulators in TMEM (two 256-column buffers, alternating by
-//                                     layer); tcgen05.commit releases ring slots / publishes accumulators;
-//       warps 2-5 epilogue         -- thread == row: encode the tile's points (sin/cos by double-angle
-//                                     recurrence) straight into the swizzled A-operand layout, then per layer
-//                                     tcgen05.ld the accumulator 64 columns at a time, add bias, ReLU, pack to
-//                                     bf16 and store it as the next layer's A operand.  Each finished
-//                                     64-column block is published on its own mbarrier, so the next layer's
-//                                     MMAs start on block 0 while blocks 1..3 are still being converted.
+//   * one CTA per SM, persistent over a contiguous range of tiles taken two at a time; 18 warps with fixed roles:
+//       warp 0     weight producer -- streams pre-swizzled 16-bit weight chunks (<= 256 N-rows x 32 K-elements, the
+//                                     exact UMMA SWIZZLE_64B K-major image) from L2 into a 3-slot shared-memory ring
+//                                     with bulk async copies (cp.async.bulk -> UBLKCP) completing on mbarriers;
+//       warp 1     MMA issuer      -- one thread issues tcgen05.mma (kind::f16, M=128, N<=256, K=16): every ring slot
+//                                     feeds BOTH tiles of the pair (A = that tile's activations in shared memory,
+//                                     D = that tile's 256 fp32 TMEM columns), halving the weight traffic per point;
+//                                     tcgen05.commit releases ring slots / publishes the accumulators;
+//       warps 2-17 epilogue        -- 8 warps per tile (TMEM lane quarter x column-block parity), thread == row:
+//                                     encode the tile's points (sin/cos by double-angle recurrence) straight into the
+//                                     swizzled A-operand layout, then per layer tcgen05.ld 64 accumulator columns,
+//                                     add bias, ReLU, pack to 16 bit and store them as the next layer's A operand.
+//                                     Each finished 64-column block is published on its own mbarrier and the
+//                                     accumulator is handed back as soon as the last tcgen05.ld has landed, so the
+//                                     next layer's MMAs start while the remaining blocks are still being converted.
 //   * the skip concat ([pts, h], K = 64 + 256) and the view-direction concat ([feat, dirs]) are extra
-//     K-blocks fed from the resident encoding tiles, not copies; alpha (N=1) rides along the
-//     bottleneck / fc_feat GEMM as extra output columns; rgb is an N=16 MMA.
+//     K-blocks fed from the resident encoding block (position encoding first; re-filled with the direction
+//     encoding once the skip layer has consumed it); alpha (N=1) is an fp32 dot product in the epilogue of the
+//     last trunk layer; rgb is an N=16 MMA.
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+
 #include <algorithm>
 #include <vector>
 
@@ -50,7 +56,10 @@ __global__ void pack_weights_kernel(const float* __restrict__ params, const Pack
   pk.y = pack_h2(v[2], v[3], false);
   pk.z = pack_h2(v[4], v[5], false);
   pk.w = pack_h2(v[6], v[7], false);
-  *reinterpret_cast<uint4*>(out + sg.dst_off + (long long)n * 128 + ((c ^ (n & 7)) << 4)) = pk;
+  // K-block = two half-blocks of 32 elements: [chunk_rows x 64 B] each, SWIZZLE_64B (16-byte chunk ^= (row >> 1) & 3)
+  const int h = c >> 2, c4 = c & 3;
+  *reinterpret_cast<uint4*>(out + sg.dst_off + (long long)h * sg.chunk_rows * 64 + (long long)n * 64 +
+                            ((c4 ^ ((n >> 1) & 3)) << 4)) = pk;
 }
 
 __global__ void pack_bias_kernel(const float* __restrict__ params, const BiasSeg* __restrict__ segs,
@@ -72,9 +81,11 @@ struct TcSrc {
   int per_dir;
 };
 
-// Encode one 3-vector into 64 fp16 channels [v, sin(2^0 v), cos(2^0 v), ...] and store them as row `row` of a
-// SWIZZLE_128B K-block.  Higher octaves by the double-angle recurrence from one accurate sincosf per component:
-// the absolute error doubles per octave (<= 2^9 * 6e-8), far below the fp16 quantum (4.9e-4) of the stored value.
+// Encode one 3-vector into 64 fp16 channels [v, sin(2^0 v), cos(2^0 v), ...] and store 16-byte chunks
+// [kChunk0, kChunk0 + kChunks) of them as row `row` of a SWIZZLE_128B K-block.  Higher octaves by the double-angle
+// recurrence from one accurate sincosf per component: the absolute error doubles per octave (<= 2^9 * 6e-8), far
+// below the fp16 quantum (4.9e-4) of the stored value.
+template <int kChunk0, int kChunks>
 __device__ __forceinline__ void encode_row(unsigned char* block, int row, float x0, float x1, float x2, int L) {
   float s[3], c[3];
   sincosf(x0, &s[0], &c[0]);
@@ -97,7 +108,7 @@ __device__ __forceinline__ void encode_row(unsigned char* block, int row, float 
   ch[63] = 0.0f;
   unsigned char* rp = block + row * 128;
 #pragma unroll
-  for (int q = 0; q < 8; ++q) {
+  for (int q = kChunk0; q < kChunk0 + kChunks; ++q) {
     uint4 pk;
     pk.x = pack_h2(ch[8 * q + 0], ch[8 * q + 1], false);
     pk.y = pack_h2(ch[8 * q + 2], ch[8 * q + 3], false);
@@ -107,48 +118,133 @@ __device__ __forceinline__ void encode_row(unsigned char* block, int row, float 
   }
 }
 
+// shared-memory accesses of the epilogue by shared-space address; volatile keeps the bias loads where they are
+// written (after tcgen05.wait::ld) instead of hoisted above the accumulator load, which would spill
+__device__ __forceinline__ float4 lds_f4(uint32_t saddr) {
+  float4 v;
+  asm volatile("ld.shared.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(saddr));
+  return v;
+}
+__device__ __forceinline__ void sts_u4(uint32_t saddr, const uint4& v) {
+  asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};" ::"r"(saddr), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+}
+// accumulator columns [c0, c0+32) of one row (+ bias, optional ReLU) -> 16-bit -> four swizzled 16-byte chunks of the
+// row's 128-byte line at rp; kAlpha also accumulates <activation, alpha weights> in fp32
+template <bool kAlpha>
+__device__ __forceinline__ void epi_convert32(const uint32_t (&v)[64], int c0, uint32_t rp, uint32_t bj, uint32_t wa, int sw,
+                                              bool relu, float& adot) {
+#pragma unroll
+  for (int c = 0; c < 4; ++c) {
+    const int e0 = c0 + 8 * c;
+    const float4 b0 = lds_f4(bj + 4 * e0), b1 = lds_f4(bj + 4 * e0 + 16);
+    const float a0 = __uint_as_float(v[e0 + 0]) + b0.x, a1 = __uint_as_float(v[e0 + 1]) + b0.y;
+    const float a2 = __uint_as_float(v[e0 + 2]) + b0.z, a3 = __uint_as_float(v[e0 + 3]) + b0.w;
+    const float a4 = __uint_as_float(v[e0 + 4]) + b1.x, a5 = __uint_as_float(v[e0 + 5]) + b1.y;
+    const float a6 = __uint_as_float(v[e0 + 6]) + b1.z, a7 = __uint_as_float(v[e0 + 7]) + b1.w;
+    if (kAlpha) {
+      const float4 w0 = lds_f4(wa + 4 * e0), w1 = lds_f4(wa + 4 * e0 + 16);
+      const float lo = relu ? 0.0f : -3.0e38f;
+      adot = fmaf(fmaxf(a0, lo), w0.x, adot); adot = fmaf(fmaxf(a1, lo), w0.y, adot);
+      adot = fmaf(fmaxf(a2, lo), w0.z, adot); adot = fmaf(fmaxf(a3, lo), w0.w, adot);
+      adot = fmaf(fmaxf(a4, lo), w1.x, adot); adot = fmaf(fmaxf(a5, lo), w1.y, adot);
+      adot = fmaf(fmaxf(a6, lo), w1.z, adot); adot = fmaf(fmaxf(a7, lo), w1.w, adot);
+    }
+    uint4 pk;
+    pk.x = pack_h2(a0, a1, relu);
+    pk.y = pack_h2(a2, a3, relu);
+    pk.z = pack_h2(a4, a5, relu);
+    pk.w = pack_h2(a6, a7, relu);
+    sts_u4(rp + ((((c0 >> 3) + c) ^ sw) << 4), pk);
+  }
+}
+
+__device__ __forceinline__ bool elect_one() {
+  uint32_t pred;
+  asm volatile("{\n.reg .pred p;\nelect.sync _|p, 0xffffffff;\nselp.u32 %0, 1, 0, p;\n}" : "=r"(pred));
+  return pred != 0;
+}
+
+__device__ long long g_fwd_dbg[8];  // NB_FWD_DEBUG & 16: cycles the MMA issuer of CTA 0 spent per wait kind
+
+// flags of the MMA issuer's step program
+enum : uint32_t { PF_WAIT_ACT = 4u, PF_WAIT_ENCD = 8u, PF_FIRST = 16u, PF_LAST = 32u, PF_ACC = 64u };
+// constant upper halves of the shared-memory operand descriptors (see umma_desc / umma_desc_sw64)
+constexpr uint64_t kDescHiSw128 = ((uint64_t)1 << 16) | ((uint64_t)(1024 >> 4) << 32) | ((uint64_t)1 << 46) | ((uint64_t)2 << 61);
+constexpr uint64_t kDescHiSw64 = ((uint64_t)1 << 16) | ((uint64_t)(512 >> 4) << 32) | ((uint64_t)1 << 46) | ((uint64_t)4 << 61);
+
 // ------------------------------------------------------------------------------------ the kernel
 __global__ void __launch_bounds__(kThreadsTc, 1)
 mlp_tc_kernel(const __grid_constant__ TcPlan plan, const unsigned char* __restrict__ wpk, const float* __restrict__ bias_g,
-              TcSrc src, long long n_points, float* __restrict__ raw, unsigned char* __restrict__ rec) {
+              TcSrc src, long long n_points, float* __restrict__ raw, unsigned char* __restrict__ rec, int dbg) {
   extern __shared__ __align__(1024) unsigned char smem_raw[];
   // carve (all tile regions 1024-byte aligned for SWIZZLE_128B)
   unsigned char* smem = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
-  unsigned char* act = smem;
-  unsigned char* encx = act + plan.n_act_blocks * kBlockBytes;
-  unsigned char* encd = encx + kBlockBytes;
-  unsigned char* ring = encd + kBlockBytes;
-  float* bias_s = reinterpret_cast<float*>(ring + kRing * plan.ring_stage_bytes);
-  uint64_t* bars = reinterpret_cast<uint64_t*>(bias_s + ((plan.n_bias + 3) & ~3));
-  // barrier indices
-  //   [0,kRing) full, [kRing,2kRing) empty, then enc_ready, act_ready[4], acc_full[2]
-  uint64_t* bar_full = bars;
-  uint64_t* bar_empty = bars + kRing;
-  uint64_t* bar_enc = bars + 2 * kRing;
-  uint64_t* bar_act = bar_enc + 1;
-  uint64_t* bar_acc = bar_act + 4;
+  const int tile_blocks = plan.n_act_blocks + 1;             // activation blocks + the encoding block
+  const int tile_bytes = tile_blocks * kBlockBytes;
+  unsigned char* act = smem;                                 // [2 tiles][tile_blocks][16 KB]
+  unsigned char* ring = act + 2 * tile_bytes;
+  float* bias_s = reinterpret_cast<float*>(ring + kFwdRing * kFwdSlotBytes);
+  float* alpha_part = bias_s + ((plan.n_bias + 3) & ~3);     // [2 tiles][2 parities][128 rows]
+  uint64_t* bars = reinterpret_cast<uint64_t*>(alpha_part + 2 * 2 * kTileM);
+  uint64_t* bar_full = bars;                   // [kFwdRing]
+  uint64_t* bar_empty = bar_full + kFwdRing;   // [kFwdRing]
+  uint64_t* bar_enc = bar_empty + kFwdRing;    // [2]  position encoding of tile t written (256 arrivals)
+  uint64_t* bar_encd = bar_enc + 2;            // [2]  direction encoding of tile t written (128)
+  uint64_t* bar_act = bar_encd + 2;            // [2][4] activation block j of tile t written (128)
+  uint64_t* bar_drain = bar_act + 8;           // [2]  accumulator of tile t read out by all 8 warps (256)
+  uint64_t* bar_acc = bar_drain + 2;           // [2]  accumulator of tile t's current stage complete
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bar_acc + 2);
+  uint4* prog = reinterpret_cast<uint4*>(tmem_slot + 4);   // [n_steps] MMA issuer program, one entry per ring slot
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const long long n_tiles = (n_points + kTileM - 1) / kTileM;
+  // contiguous, balanced tile range of this CTA; taken two tiles at a time, a trailing single tile runs alone
+  const long long tile_begin = n_tiles * blockIdx.x / gridDim.x;
+  const long long tile_end = n_tiles * (blockIdx.x + 1) / gridDim.x;
 
   if (threadIdx.x == 0) {
-    for (int i = 0; i < kRing; ++i) {
+    for (int i = 0; i < kFwdRing; ++i) {
       mbar_init(smem_u32(bar_full + i), 1);
-      mbar_init(smem_u32(bar_empty + i), 1);
+      mbar_init(smem_u32(bar_empty + i), 2);   // one commit per MMA issuer warp
     }
-    mbar_init(smem_u32(bar_enc), 128);
-    for (int i = 0; i < 4; ++i) mbar_init(smem_u32(bar_act + i), 128);
-    mbar_init(smem_u32(bar_acc), 1);
-    mbar_init(smem_u32(bar_acc + 1), 1);
+    for (int t = 0; t < 2; ++t) {
+      mbar_init(smem_u32(bar_acc + t), 1);
+      mbar_init(smem_u32(bar_enc + t), 256);
+      mbar_init(smem_u32(bar_encd + t), 128);
+      for (int i = 0; i < 4; ++i) mbar_init(smem_u32(bar_act + 4 * t + i), 128);
+      mbar_init(smem_u32(bar_drain + t), 256);
+    }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
-  if (warp == 1) {  // TMEM: all 512 columns (one CTA per SM)
+  if (threadIdx.x == 96) {
+    // step program: x = byte offset of the A operand half-block inside a tile's region, y = instruction descriptor,
+    // z = flags (PF_*; bits 0-1 = activation block to wait for), w = X-record block the awaited operand is saved to
+    int i = 0;
+    for (int s = 0; s < plan.n_stages; ++s) {
+      const TcStage& st = plan.st[s];
+      for (int kb = 0; kb < st.n_kb; ++kb) {
+        const int sidx = st.a_src[kb];
+        for (int h = 0; h < 2; ++h) {
+          uint4 e;
+          e.x = (uint32_t)((sidx < 4 ? sidx : plan.n_act_blocks) * kBlockBytes + h * 64);
+          e.y = umma_idesc(st.n_main);
+          e.z = 0u;
+          e.w = 0u;
+          if (h == 0 && sidx < 4) { e.z |= PF_WAIT_ACT | (uint32_t)sidx; e.w = (uint32_t)(plan.st[s - 1].rec_blk + sidx); }
+          if (h == 0 && sidx == SRC_ENCD) { e.z |= PF_WAIT_ENCD; e.w = 1u; }
+          if (kb == 0 && h == 0) e.z |= PF_FIRST;
+          if (kb == st.n_kb - 1 && h == 1) e.z |= PF_LAST;
+          if ((kb | h) != 0) e.z |= PF_ACC;
+          prog[i++] = e;
+        }
+      }
+    }
+  }
+  if (warp == 1) {  // TMEM: all 512 columns (one CTA per SM): tile t owns columns [256 t, 256 t + 256)
     asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "r"(512));
     asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
   }
   for (int i = threadIdx.x; i < plan.n_bias; i += blockDim.x) bias_s[i] = bias_g[i];
-  // encoding tiles: padding columns are rewritten every tile by encode_row, nothing to clear
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -158,92 +254,131 @@ mlp_tc_kernel(const __grid_constant__ TcPlan plan, const unsigned char* __restri
     // ============================ weight producer ============================
     if (lane == 0) {
       uint32_t slot = 0, phase = 0;
-      for (long long tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+      for (long long tile = tile_begin; tile < tile_end; tile += 2) {
         for (int s = 0; s < plan.n_stages; ++s) {
           const TcStage& st = plan.st[s];
           for (int kb = 0; kb < st.n_kb; ++kb) {
-            mbar_wait(smem_u32(bar_empty + slot), phase ^ 1);
-            const uint32_t fb = smem_u32(bar_full + slot);
-            mbar_expect_tx(fb, (uint32_t)st.chunk_bytes);
-            bulk_g2s(smem_u32(ring + slot * plan.ring_stage_bytes), wpk + st.w_off + (size_t)kb * st.chunk_bytes,
-                     (uint32_t)st.chunk_bytes, fb);
-            if (++slot == kRing) { slot = 0; phase ^= 1; }
+            for (int h = 0; h < 2; ++h) {
+              const uint32_t bytes = (uint32_t)st.n_main * 64u;
+              mbar_wait(smem_u32(bar_empty + slot), phase ^ 1);
+              const uint32_t fb = smem_u32(bar_full + slot);
+              if (dbg & 1) { mbar_arrive(fb); if (++slot == kFwdRing) { slot = 0; phase ^= 1; } continue; }
+              mbar_expect_tx(fb, bytes);
+              bulk_g2s(smem_u32(ring + slot * kFwdSlotBytes), wpk + st.w_off + (size_t)kb * st.chunk_bytes + (size_t)h * bytes,
+                       bytes, fb);
+              if (++slot == kFwdRing) { slot = 0; phase ^= 1; }
+            }
           }
         }
       }
     }
-  } else if (warp == 1) {
-    // ============================ MMA issuer ============================
-    if (lane == 0) {
-      uint32_t slot = 0, phase = 0, enc_phase = 0;
-      uint32_t act_phase[4] = {0, 0, 0, 0};
-      for (long long tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
-        mbar_wait(smem_u32(bar_enc), enc_phase);
-        enc_phase ^= 1;
+  } else if (warp == 1 || warp == 2) {
+    // ============================ MMA issuers (one warp per tile of the pair) ============================
+    // The whole warp walks the per-pair step program (one entry per ring slot, built in shared memory at kernel
+    // start) in warp-uniform control flow, so descriptors and phases live in uniform registers; only the tcgen05 /
+    // bulk-copy instructions are predicated on one elected lane.  The issue loop has to stay far below the 256
+    // tensor cycles one slot feeds per tile, or the tensor pipe starves (measured: tools/umma_bench.cu).
+    const int t = warp - 1;
+    uint32_t slot = 0, phase = 0;
+    uint32_t ph_act = 0;     // bit j: parity of bar_act[t][j]
+    uint32_t ph_enc = 0, ph_encd = 0, ph_drain = 0;
+    bool armed = false;      // an epilogue of this tile slot has run: its accumulator hand-back must be awaited
+    const uint32_t act_s = smem_u32(act) + t * tile_bytes, ring_s = smem_u32(ring);
+    const uint32_t bar_full_s = smem_u32(bar_full), bar_empty_s = smem_u32(bar_empty), bar_act_s = smem_u32(bar_act + 4 * t);
+    const uint32_t bar_enc_s = smem_u32(bar_enc + t), bar_encd_s = smem_u32(bar_encd + t);
+    const uint32_t bar_drain_s = smem_u32(bar_drain + t), bar_acc_s = smem_u32(bar_acc + t);
+    const uint32_t enc_off = plan.n_act_blocks * kBlockBytes;
+    const uint32_t d_tmem = tmem_base + t * 256;
+    const int n_steps = plan.n_steps;
+    const size_t rec_stride = (size_t)plan.rec_blocks * kBlockBytes;
+    for (long long tile0 = tile_begin; tile0 < tile_end; tile0 += 2) {
+      if (tile0 + t >= tile_end) {
+        // trailing single tile: this issuer only keeps the ring's two-commit protocol going
+        for (int i = 0; i < n_steps; ++i) {
+          mbar_wait(bar_full_s + 8 * slot, phase);
+          if (elect_one()) tc_commit(bar_empty_s + 8 * slot);
+          __syncwarp();
+          if (++slot == kFwdRing) { slot = 0; phase ^= 1; }
+        }
+        break;
+      }
+      // train: every operand block is also written to the per-tile X record, in the exact swizzled image the
+      // backward kernels load (K-major for recompute-free dgrad masks, MN-major operand of the wgrad MMAs)
+      unsigned char* rec_t = rec ? rec + (size_t)(tile0 + t) * rec_stride : nullptr;
+      mbar_wait(bar_enc_s, ph_enc);
+      ph_enc ^= 1;
+      if (rec && elect_one()) {
+        bulk_s2g(rec_t, act_s + enc_off, kBlockBytes);
+        bulk_commit();
+      }
+      __syncwarp();
+      uint4 e = prog[0];
+      for (int i = 0; i < n_steps; ++i) {
+        const uint4 en = prog[i + 1 < n_steps ? i + 1 : i];  // prefetch
+        const uint32_t fl = e.z;
+        if (fl & (PF_WAIT_ACT | PF_WAIT_ENCD)) {
+          if (fl & PF_WAIT_ACT) {
+            const uint32_t j = fl & 3u;
+            mbar_wait(bar_act_s + 8 * j, (ph_act >> j) & 1u);
+            ph_act ^= 1u << j;
+          } else {
+            mbar_wait(bar_encd_s, ph_encd);
+            ph_encd ^= 1;
+          }
+          if (rec && elect_one()) {
+            bulk_s2g(rec_t + (size_t)e.w * kBlockBytes, act_s + (e.x & ~127u), kBlockBytes);
+            bulk_commit();
+          }
+          __syncwarp();
+        }
+        if ((fl & PF_FIRST) && armed) {  // the previous stage's epilogue has read this tile's accumulator out
+          mbar_wait(bar_drain_s, ph_drain);
+          ph_drain ^= 1;
+        }
+        armed = true;
+        mbar_wait(bar_full_s + 8 * slot, phase);
         tc_fence_after();
-        // train: every operand tile is also written to the per-tile X record, in the exact swizzled image the
-        // backward kernels load (K-major for recompute-free dgrad masks, MN-major operand of the wgrad MMAs)
-        unsigned char* rec_tile = rec ? rec + (size_t)tile * plan.rec_blocks * kBlockBytes : nullptr;
-        if (rec_tile) {
-          bulk_s2g(rec_tile, smem_u32(encx), kBlockBytes);
-          if (plan.Cd > 0) bulk_s2g(rec_tile + kBlockBytes, smem_u32(encd), kBlockBytes);
-          bulk_commit();
-        }
-        for (int s = 0; s < plan.n_stages; ++s) {
-          const TcStage& st = plan.st[s];
-          const int buf = s & 1;
-          const uint32_t d_main = tmem_base + buf * 256;
-          const uint32_t d_extra = tmem_base + (buf ^ 1) * 256;
-          const uint32_t idesc_main = umma_idesc(st.n_main);
-          const uint32_t idesc_extra = umma_idesc(16);
-          for (int kb = 0; kb < st.n_kb; ++kb) {
-            const int sidx = st.a_src[kb];
-            uint32_t a_base;
-            if (sidx < 4) {
-              mbar_wait(smem_u32(bar_act + sidx), act_phase[sidx]);
-              act_phase[sidx] ^= 1;
-              tc_fence_after();
-              a_base = smem_u32(act + sidx * kBlockBytes);
-              if (rec_tile) {
-                bulk_s2g(rec_tile + (size_t)(plan.st[s - 1].rec_blk + sidx) * kBlockBytes, a_base, kBlockBytes);
-                bulk_commit();
-              }
-            } else {
-              a_base = smem_u32(sidx == SRC_ENCX ? encx : encd);
-            }
-            mbar_wait(smem_u32(bar_full + slot), phase);
-            tc_fence_after();
-            const uint32_t b_base = smem_u32(ring + slot * plan.ring_stage_bytes);
-#pragma unroll
-            for (int k = 0; k < 4; ++k) {
-              const uint32_t accum = (kb | k) != 0 ? 1u : 0u;
-              tc_mma(d_main, umma_desc(a_base + k * 32), umma_desc(b_base + k * 32), idesc_main, accum);
-              if (st.n_extra)
-                tc_mma(d_extra, umma_desc(a_base + k * 32), umma_desc(b_base + st.n_main * 128 + k * 32), idesc_extra,
-                       accum);
-            }
-            tc_commit(smem_u32(bar_empty + slot));  // frees the ring slot when these MMAs have read it
-            if (++slot == kRing) { slot = 0; phase ^= 1; }
+        const uint64_t a_desc = kDescHiSw128 | (uint64_t)(((act_s + e.x) & 0x3FFFFu) >> 4);
+        const uint64_t b_desc = kDescHiSw64 | (uint64_t)(((ring_s + slot * kFwdSlotBytes) & 0x3FFFFu) >> 4);
+        if (elect_one()) {
+          tc_mma(d_tmem, a_desc, b_desc, e.y, (fl & PF_ACC) ? 1u : 0u);
+          tc_mma(d_tmem, a_desc + 2, b_desc + 2, e.y, 1u);
+          tc_commit(bar_empty_s + 8 * slot);  // (1 of 2 arrivals) frees the ring slot when these MMAs have read it
+          if (fl & PF_LAST) {
+            if (rec) bulk_wait_read0();  // record stores have read the blocks this stage's epilogue overwrites
+            tc_commit(bar_acc_s);        // accumulator of this stage complete
           }
-          if (rec_tile) bulk_wait_read0();     // record stores have read the tiles this stage's epilogue overwrites
-          tc_commit(smem_u32(bar_acc + buf));  // accumulator of this stage complete
         }
+        __syncwarp();
+        if (++slot == kFwdRing) { slot = 0; phase ^= 1; }
+        e = en;
       }
-      if (rec) bulk_wait0();
     }
-  } else {
+    if (rec && elect_one()) bulk_wait0();
+    __syncwarp();
+  } else if (warp >= 4) {
     // ============================ epilogue warps (thread == row) ============================
+    const int e = warp - 4;
+    const int t = e >> 3;               // tile of the pair
+    const int par = (e >> 2) & 1;       // handles 64-column blocks j == par (mod 2)
     const int q = warp & 3;             // TMEM lane quarter this warp may access
     const int row = q * 32 + lane;      // row of the tile
-    const uint32_t lane_addr = ((uint32_t)(q * 32)) << 16;
-    uint32_t acc_phase[2] = {0, 0};
-    for (long long tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+    const int sw = row & 7;
+    const uint32_t t_main = tmem_base + (((uint32_t)(q * 32)) << 16) + t * 256;
+    unsigned char* act_t = act + t * tile_bytes;
+    unsigned char* enc_t = act_t + plan.n_act_blocks * kBlockBytes;
+    float* apart = alpha_part + (t * 2 + par) * kTileM;
+    uint32_t acc_phase = 0;
+    for (long long tile0 = tile_begin; tile0 < tile_end; tile0 += 2) {
+      const long long tile = tile0 + t;
+      if (tile >= tile_end) break;      // trailing single tile: the second half of the CTA sits it out
       long long p = tile * kTileM + row;
       const bool in_range = p < n_points;
       if (!in_range) p = n_points - 1;
-      // ---- positional encoding of this row's point and view direction
+      // ---- positional encoding of this row's point (the two parities write 4 chunks of the row each)
+      float v0 = 0.f, v1 = 0.f, v2 = 0.f;
       {
-        float x0, x1, x2, v0 = 0.f, v1 = 0.f, v2 = 0.f;
+        float x0, x1, x2;
         if (src.rays != nullptr) {
           const long long r = p / src.S;
           const float* ry = src.rays + r * src.stride;
@@ -251,40 +386,36 @@ mlp_tc_kernel(const __grid_constant__ TcPlan plan, const unsigned char* __restri
           x0 = __fadd_rn(ry[0], __fmul_rn(ry[3], zz));
           x1 = __fadd_rn(ry[1], __fmul_rn(ry[4], zz));
           x2 = __fadd_rn(ry[2], __fmul_rn(ry[5], zz));
-          if (plan.Cd > 0) { v0 = ry[8]; v1 = ry[9]; v2 = ry[10]; }
+          if (plan.Cd > 0 && par == 1) { v0 = ry[8]; v1 = ry[9]; v2 = ry[10]; }
         } else {
           x0 = src.pts[3 * p]; x1 = src.pts[3 * p + 1]; x2 = src.pts[3 * p + 2];
-          if (plan.Cd > 0) {
+          if (plan.Cd > 0 && par == 1) {
             const float* vv = src.viewdirs + (p / src.per_dir) * 3;
             v0 = vv[0]; v1 = vv[1]; v2 = vv[2];
           }
         }
-        encode_row(encx, row, x0, x1, x2, plan.Lx);
-        if (plan.Cd > 0) encode_row(encd, row, v0, v1, v2, plan.Ld);
+        if (par == 0) encode_row<0, 4>(enc_t, row, x0, x1, x2, plan.Lx);
+        else encode_row<4, 4>(enc_t, row, x0, x1, x2, plan.Lx);
       }
-      tc_fence_before();  // our TMEM loads of the previous tile are ordered before the MMAs this arrive releases
       fence_async_smem();
-      mbar_arrive(smem_u32(bar_enc));
+      mbar_arrive(smem_u32(bar_enc + t));
 
       float alpha_raw = 0.0f;
       for (int s = 0; s < plan.n_stages; ++s) {
         const TcStage& st = plan.st[s];
-        const int buf = s & 1;
-        mbar_wait(smem_u32(bar_acc + buf), acc_phase[buf]);
-        acc_phase[buf] ^= 1;
+        mbar_wait(smem_u32(bar_acc + t), acc_phase);
+        acc_phase ^= 1;
         tc_fence_after();
-        const uint32_t t_main = tmem_base + lane_addr + buf * 256;
         const float* bs = bias_s + st.b_off;
-        if (st.epi == EPI_HEAD) {
-          const uint32_t ta = st.alpha_col >= 0 ? t_main + st.alpha_col : tmem_base + lane_addr + (buf ^ 1) * 256;
-          const uint32_t a = tmem_ld1(ta);
-          tc_wait_ld();
-          alpha_raw = __uint_as_float(a) + bs[st.n_act];
-        }
-        if (st.epi == EPI_HIDDEN || st.epi == EPI_HEAD) {
+        if (st.epi == EPI_HIDDEN) {
           const bool relu = st.relu != 0;
           const int nblk = st.n_act >> 6;
-          for (int j = 0; j < nblk; ++j) {
+          float adot = 0.0f;
+          if (par >= nblk) {  // nothing to read in this stage
+            tc_fence_before();
+            mbar_arrive(smem_u32(bar_drain + t));
+          }
+          for (int j = par; j < nblk; j += 2) {
             uint32_t v[64];
             NB_TMEM_LD32(t_main + j * 64, v);
             {
@@ -292,33 +423,54 @@ mlp_tc_kernel(const __grid_constant__ TcPlan plan, const unsigned char* __restri
               NB_TMEM_LD32(t_main + j * 64 + 32, v2);
             }
             tc_wait_ld();
-            unsigned char* rp = act + j * kBlockBytes + row * 128;
-            const float* bj = bs + j * 64;
-#pragma unroll
-            for (int c = 0; c < 8; ++c) {
-              const float4 b0 = *reinterpret_cast<const float4*>(bj + 8 * c);
-              const float4 b1 = *reinterpret_cast<const float4*>(bj + 8 * c + 4);
-              uint4 pk;
-              pk.x = pack_h2(__uint_as_float(v[8 * c + 0]) + b0.x, __uint_as_float(v[8 * c + 1]) + b0.y, relu);
-              pk.y = pack_h2(__uint_as_float(v[8 * c + 2]) + b0.z, __uint_as_float(v[8 * c + 3]) + b0.w, relu);
-              pk.z = pack_h2(__uint_as_float(v[8 * c + 4]) + b1.x, __uint_as_float(v[8 * c + 5]) + b1.y, relu);
-              pk.w = pack_h2(__uint_as_float(v[8 * c + 6]) + b1.z, __uint_as_float(v[8 * c + 7]) + b1.w, relu);
-              *reinterpret_cast<uint4*>(rp + ((c ^ (row & 7)) << 4)) = pk;
+            if (j + 2 >= nblk) {  // last accumulator read of this stage: hand the TMEM columns back
+              tc_fence_before();
+              mbar_arrive(smem_u32(bar_drain + t));
             }
-            tc_fence_before();
+            if (dbg & 2) { fence_async_smem(); mbar_arrive(smem_u32(bar_act + 4 * t + j)); continue; }
+            const uint32_t rp = smem_u32(act_t) + j * kBlockBytes + row * 128;
+            const uint32_t bj = smem_u32(bs) + j * 256;
+            if (st.alpha_dot) {
+              const uint32_t wa = smem_u32(bias_s) + (plan.alpha_w_off + j * 64) * 4;
+              epi_convert32<true>(v, 0, rp, bj, wa, sw, relu, adot);
+              epi_convert32<true>(v, 32, rp, bj, wa, sw, relu, adot);
+            } else {
+              epi_convert32<false>(v, 0, rp, bj, 0u, sw, relu, adot);
+              epi_convert32<false>(v, 32, rp, bj, 0u, sw, relu, adot);
+            }
             fence_async_smem();
-            mbar_arrive(smem_u32(bar_act + j));
+            mbar_arrive(smem_u32(bar_act + 4 * t + j));
+          }
+          if (st.alpha_dot) apart[row] = adot;
+          if (st.write_encd && par == 1) {
+            // every MMA reading the position encoding has completed (bar_acc of this stage): the block now
+            // becomes the direction encoding for the view-dependent layer
+            encode_row<0, 8>(enc_t, row, v0, v1, v2, plan.Ld);
+            fence_async_smem();
+            mbar_arrive(smem_u32(bar_encd + t));
           }
         } else {
-          uint32_t v[4];
-          tmem_ld4(t_main, v);
-          tc_wait_ld();
-          float4 o;
-          o.x = __uint_as_float(v[0]) + bs[0];
-          o.y = __uint_as_float(v[1]) + bs[1];
-          o.z = __uint_as_float(v[2]) + bs[2];
-          o.w = st.epi == EPI_RGB ? alpha_raw : __uint_as_float(v[3]) + bs[3];
-          if (in_range) reinterpret_cast<float4*>(raw)[tile * kTileM + row] = o;
+          uint32_t v[4] = {0u, 0u, 0u, 0u};
+          if (par == 0) {
+            tmem_ld4(t_main, v);
+            tc_wait_ld();
+          }
+          tc_fence_before();
+          mbar_arrive(smem_u32(bar_drain + t));
+          if (par == 0) {
+            float4 o;
+            o.x = __uint_as_float(v[0]) + bs[0];
+            o.y = __uint_as_float(v[1]) + bs[1];
+            o.z = __uint_as_float(v[2]) + bs[2];
+            if (st.epi == EPI_RGB) {
+              const float* ap = alpha_part + (t * 2) * kTileM;
+              alpha_raw = ap[row] + ap[kTileM + row] + bias_s[plan.alpha_b_off];
+              o.w = alpha_raw;
+            } else {
+              o.w = __uint_as_float(v[3]) + bs[3];
+            }
+            if (in_range) reinterpret_cast<float4*>(raw)[tile * kTileM + row] = o;
+          }
         }
       }
     }
@@ -354,26 +506,26 @@ static bool build_plan(const Graph& g, TcPlan& plan, std::vector<PackSeg>& segs,
   const int wb = g.width / 64;
   plan.n_act_blocks = std::max(wb, g.use_viewdirs ? g.feat_width / 64 : 0);
   plan.Cx = g.Cx; plan.Cd = g.Cd; plan.Lx = g.n_freq_xyz; plan.Ld = g.n_freq_dir;
+  plan.alpha_w_off = plan.alpha_b_off = -1;
   plan.rec_blocks = 2;  // [encx, encd]
   size_t woff = 0;
-  int boff = 0, ring_max = 0;
-  auto begin_stage = [&](int n_main, int n_extra, int epi, int relu, int n_act, int alpha_col) -> TcStage& {
+  int boff = 0;
+  auto begin_stage = [&](int n_main, int epi, int relu, int n_act) -> TcStage& {
     TcStage& st = plan.st[plan.n_stages++];
     st.n_kb = 0;
-    st.n_main = n_main; st.n_extra = n_extra; st.chunk_bytes = (n_main + n_extra) * 128;
-    st.w_off = (int)woff; st.b_off = boff; st.epi = epi; st.relu = relu; st.n_act = n_act; st.alpha_col = alpha_col;
+    st.n_main = n_main; st.chunk_bytes = n_main * 128;
+    st.w_off = (int)woff; st.b_off = boff; st.epi = epi; st.relu = relu; st.n_act = n_act;
+    st.alpha_dot = 0; st.write_encd = 0;
     st.rec_blk = plan.rec_blocks;
     plan.rec_blocks += n_act / 64;
-    boff += (n_main + n_extra + 3) & ~3;
-    ring_max = std::max(ring_max, st.chunk_bytes);
+    boff += (n_main + 3) & ~3;
     return st;
   };
-  // adds one K-block to the stage: rows from up to two source matrices
-  auto add_kb = [&](TcStage& st, int a_src, std::initializer_list<PackSeg> rows) {
-    for (PackSeg sg : rows) {
-      sg.dst_off = (long long)woff;
-      segs.push_back(sg);
-    }
+  // adds one K-block to the stage
+  auto add_kb = [&](TcStage& st, int a_src, PackSeg sg) {
+    sg.dst_off = (long long)woff;
+    sg.chunk_rows = st.n_main;
+    segs.push_back(sg);
     st.a_src[st.n_kb++] = a_src;
     woff += st.chunk_bytes;
   };
@@ -383,19 +535,21 @@ static bool build_plan(const Graph& g, TcPlan& plan, std::vector<PackSeg>& segs,
     return s;
   };
   if (g.depth + 3 > kMaxStages) { *why = "too many layers"; return false; }
+  int last_encx = 0;
   for (int i = 0; i < g.depth; ++i) {
     const Lin& l = g.lins[g.trunk[i]];
-    TcStage& st = begin_stage(g.width, 0, EPI_HIDDEN, !(i == 0 && !g.act0), g.width, 0);
+    TcStage& st = begin_stage(g.width, EPI_HIDDEN, !(i == 0 && !g.act0), g.width);
     bsegs.push_back(BiasSeg{st.b_off, l.out, l.b_off});
     if (i == 0) {
-      add_kb(st, SRC_ENCX, {seg(l, 0, 0, g.Cx)});
+      add_kb(st, SRC_ENCX, seg(l, 0, 0, g.Cx));
     } else {
       int off = 0;
       if (i - 1 == g.skip) {
-        add_kb(st, SRC_ENCX, {seg(l, 0, 0, g.Cx)});
+        add_kb(st, SRC_ENCX, seg(l, 0, 0, g.Cx));
         off = g.Cx;
+        last_encx = i;
       }
-      for (int j = 0; j < wb; ++j) add_kb(st, j, {seg(l, 0, off + 64 * j, 64)});
+      for (int j = 0; j < wb; ++j) add_kb(st, j, seg(l, 0, off + 64 * j, 64));
     }
   }
   if (g.use_viewdirs) {
@@ -404,40 +558,49 @@ static bool build_plan(const Graph& g, TcPlan& plan, std::vector<PackSeg>& segs,
     const Lin& ld = g.lins[g.dir];
     const Lin& lr = g.lins[g.rgb];
     if (g.dir_width % 64 != 0) { *why = "direction layer width must be a multiple of 64"; return false; }
-    const bool split = g.feat_width + 16 > 256;
-    TcStage& sh = begin_stage(split ? g.feat_width : g.feat_width + 16, split ? 16 : 0, EPI_HEAD, g.feat_act ? 1 : 0,
-                              g.feat_width, split ? -1 : g.feat_width);
+    // alpha = <h_last, w_alpha> + b_alpha in the epilogue of the last trunk layer (fp32 weights next to the biases)
+    plan.st[g.depth - 1].alpha_dot = 1;
+    plan.alpha_w_off = boff;
+    bsegs.push_back(BiasSeg{boff, g.width, la.w_off});
+    boff += g.width;
+    plan.alpha_b_off = boff;
+    bsegs.push_back(BiasSeg{boff, 1, la.b_off});
+    boff += 4;
+    // the position-encoding block is dead after its last consumer: that stage's epilogue writes the direction encoding
+    plan.st[last_encx].write_encd = g.Cd > 0 ? 1 : 0;
+    TcStage& sh = begin_stage(g.feat_width, EPI_HIDDEN, g.feat_act ? 1 : 0, g.feat_width);
     bsegs.push_back(BiasSeg{sh.b_off, lf.out, lf.b_off});
-    bsegs.push_back(BiasSeg{sh.b_off + g.feat_width, 1, la.b_off});
-    for (int j = 0; j < wb; ++j) add_kb(sh, j, {seg(lf, 0, 64 * j, 64), seg(la, g.feat_width, 64 * j, 64)});
-    // direction layer: activation blocks first (its first wait also orders it after the alpha read), encoding last
-    TcStage& sd = begin_stage(g.dir_width, 0, EPI_HIDDEN, 1, g.dir_width, 0);
+    for (int j = 0; j < wb; ++j) add_kb(sh, j, seg(lf, 0, 64 * j, 64));
+    TcStage& sd = begin_stage(g.dir_width, EPI_HIDDEN, 1, g.dir_width);
     bsegs.push_back(BiasSeg{sd.b_off, ld.out, ld.b_off});
-    for (int j = 0; j < g.feat_width / 64; ++j) add_kb(sd, j, {seg(ld, 0, 64 * j, 64)});
-    add_kb(sd, SRC_ENCD, {seg(ld, 0, g.feat_width, g.Cd)});
-    TcStage& sr = begin_stage(16, 0, EPI_RGB, 0, 0, 0);
+    for (int j = 0; j < g.feat_width / 64; ++j) add_kb(sd, j, seg(ld, 0, 64 * j, 64));
+    if (g.Cd > 0) add_kb(sd, SRC_ENCD, seg(ld, 0, g.feat_width, g.Cd));
+    TcStage& sr = begin_stage(16, EPI_RGB, 0, 0);
     bsegs.push_back(BiasSeg{sr.b_off, 3, lr.b_off});
-    for (int j = 0; j < g.dir_width / 64; ++j) add_kb(sr, j, {seg(lr, 0, 64 * j, 64)});
+    for (int j = 0; j < g.dir_width / 64; ++j) add_kb(sr, j, seg(lr, 0, 64 * j, 64));
   } else {
     const Lin& lo = g.lins[g.out4];
-    TcStage& so = begin_stage(16, 0, EPI_OUT4, 0, 0, 0);
+    TcStage& so = begin_stage(16, EPI_OUT4, 0, 0);
     bsegs.push_back(BiasSeg{so.b_off, 4, lo.b_off});
-    for (int j = 0; j < wb; ++j) add_kb(so, j, {seg(lo, 0, 64 * j, 64)});
+    for (int j = 0; j < wb; ++j) add_kb(so, j, seg(lo, 0, 64 * j, 64));
   }
   for (int s = 0; s < plan.n_stages; ++s)
     if (plan.st[s].n_kb > kMaxKB) { *why = "too many K blocks"; return false; }
   plan.n_bias = boff;
-  plan.ring_stage_bytes = (int)round_up(ring_max, 1024);
+  plan.n_steps = 0;
+  for (int s = 0; s < plan.n_stages; ++s) plan.n_steps += 2 * plan.st[s].n_kb;
   w_bytes = woff;
   return true;
 }
 
 static size_t tc_smem_bytes(const TcPlan& plan) {
   size_t b = 1024;  // alignment slack
-  b += (size_t)(plan.n_act_blocks + 2) * kBlockBytes;
-  b += (size_t)kRing * plan.ring_stage_bytes;
+  b += (size_t)2 * (plan.n_act_blocks + 1) * kBlockBytes;
+  b += (size_t)kFwdRing * kFwdSlotBytes;
   b += (size_t)((plan.n_bias + 3) & ~3) * sizeof(float);
-  b += (2 * kRing + 1 + 4 + 2) * sizeof(uint64_t) + 16;
+  b += (size_t)2 * 2 * kTileM * sizeof(float);
+  b += (2 * kFwdRing + 2 + 2 + 8 + 2 + 2) * sizeof(uint64_t) + 16;
+  b += (size_t)plan.n_steps * sizeof(uint4);
   return b;
 }
 
@@ -524,8 +687,19 @@ int tc_forward(const nb_model* m, const float* rays, int ray_stride, const float
   }
   TcSrc src{rays, ray_stride, z_vals, n_samples > 0 ? n_samples : 1, pts, viewdirs, points_per_dir > 0 ? points_per_dir : 1};
   const int64_t n_tiles = ceil_div(n_points, kTileM);
-  const int grid = (int)std::min<int64_t>(n_tiles, sm_count());
-  mlp_tc_kernel<<<grid, kThreadsTc, p->smem_bytes, stream>>>(p->plan, p->d_w, p->d_bias, src, (long long)n_points, raw, rec);
+  const int grid = (int)std::min<int64_t>(ceil_div(n_tiles, 2), sm_count());
+  static const int dbg = getenv("NB_FWD_DEBUG") ? atoi(getenv("NB_FWD_DEBUG")) : 0;
+  mlp_tc_kernel<<<grid, kThreadsTc, p->smem_bytes, stream>>>(p->plan, p->d_w, p->d_bias, src, (long long)n_points, raw, rec, dbg);
+  if (dbg & 16) {
+    long long h[8];
+    cudaDeviceSynchronize();
+    cudaMemcpyFromSymbol(h, g_fwd_dbg, sizeof(h));
+    if (h[4] > 0)
+      fprintf(stderr, "[fwd dbg] pairs %lld: cycles/pair %lld = wait act %lld + wait full %lld + wait drain %lld + issue %lld\n", h[4],
+              h[0] / h[4], h[1] / h[4], h[2] / h[4], h[3] / h[4], (h[0] - h[1] - h[2] - h[3]) / h[4]);
+    memset(h, 0, sizeof(h));
+    cudaMemcpyToSymbol(g_fwd_dbg, h, sizeof(h));
+  }
   NB_LAUNCHED();
   return NB_OK;
 }

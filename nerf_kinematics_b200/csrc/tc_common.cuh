@@ -15,26 +15,33 @@ constexpr int kRing = 3;
 constexpr int kTileM = 128;
 constexpr int kBlockBytes = kTileM * 128;  // one 128-row x 64-element 16-bit K-block, SWIZZLE_128B
 enum { SRC_ENCX = 4, SRC_ENCD = 5, SRC_DRAW = 6 };
-enum { EPI_HIDDEN = 0, EPI_HEAD = 1, EPI_RGB = 2, EPI_OUT4 = 3 };
-constexpr int kThreadsTc = 192;
+enum { EPI_HIDDEN = 0, EPI_RGB = 2, EPI_OUT4 = 3 };
+// forward kernel: weight producer warp, 2 MMA issuer warps (one per tile), a spare warp, 2 tiles x 8 epilogue warps
+constexpr int kThreadsTc = 640;
+constexpr int kFwdRing = 3;                 // ring slots of the forward kernel
+constexpr int kFwdSlotBytes = 256 * 64;     // one slot = <= 256 weight rows (N) x 32 K-elements, SWIZZLE_64B
 
 // ---- forward plan
 struct TcStage {
   int n_kb;
   int a_src[kMaxKB];  // 0..3 activation block, SRC_ENCX, SRC_ENCD
-  int n_main;         // N of the main MMA (multiple of 16, <= 256)
-  int n_extra;        // 0 | 16: second MMA on chunk rows [n_main, n_main+16) -> other accumulator buffer, col 0
-  int chunk_bytes;    // (n_main + n_extra) * 128
-  int w_off;          // byte offset of K-block 0 in the packed weights; K-block k at w_off + k*chunk_bytes
+  int n_main;         // N of the stage's MMAs (multiple of 16, <= 256)
+  int chunk_bytes;    // n_main * 128
+  int w_off;          // byte offset of K-block 0 in the packed weights; K-block k at w_off + k*chunk_bytes, stored as
+                      // two half-blocks of 32 K-elements (n_main rows x 64 B, SWIZZLE_64B), one ring slot each
   int b_off;          // float offset of this stage's biases
   int epi, relu;
   int n_act;          // columns stored back as activations (multiple of 64)
-  int alpha_col;      // EPI_HEAD: accumulator column of alpha in this stage's buffer, -1 = other buffer col 0
+  int alpha_dot;      // 1: the epilogue also forms alpha = <activation row, alpha weights> (+ bias) in fp32
+  int write_encd;     // 1: the position-encoding block is dead after this stage's MMAs; its epilogue re-fills it
+                      //    with the direction encoding
   int rec_blk;        // train: first block of this stage's activations in the per-tile record (X record)
 };
 
 struct TcPlan {
-  int n_stages, n_act_blocks, Cx, Cd, Lx, Ld, n_bias, ring_stage_bytes;
+  int n_stages, n_act_blocks, Cx, Cd, Lx, Ld, n_bias;
+  int n_steps;        // ring slots consumed per tile pair = 2 * sum of the stages' K-blocks
+  int alpha_w_off, alpha_b_off;  // float offsets (bias buffer) of the fp32 alpha weights [width] and bias; -1 = none
   int rec_blocks;     // X record: [encx, encd, stage activations...] blocks of kBlockBytes per 128-point tile
   TcStage st[kMaxStages];
 };
@@ -87,6 +94,7 @@ struct PackSeg {
   long long dst_off;  // bytes, start of the chunk in the packed image
   long long src_off;  // floats, start of the source matrix in the flat parameters
   int row0, n_rows;   // chunk rows [row0, row0+n_rows) <- source rows [0, n_rows)
+  int chunk_rows;     // rows of the whole chunk (the stage's N)
   int ld, col0, ncols;  // source leading dim; chunk element k <- source column col0+k for k < ncols, else 0
 };
 // transposed chunk for the dgrad chain: chunk row n (layer input), element kdst0+k <- W[krow0+k, col0+n], k < kcount
@@ -208,6 +216,15 @@ __device__ __forceinline__ uint64_t umma_desc(uint32_t saddr) {
   d |= (uint64_t)(1024 >> 4) << 32;  // stride byte offset
   d |= (uint64_t)1 << 46;            // descriptor version (sm_100)
   d |= (uint64_t)2 << 61;            // SWIZZLE_128B
+  return d;
+}
+// Same for a SWIZZLE_64B K-major operand: rows of 64 B (32 elements), 8-row groups 512 B apart.
+__device__ __forceinline__ uint64_t umma_desc_sw64(uint32_t saddr) {
+  uint64_t d = (uint64_t)((saddr & 0x3FFFFu) >> 4);
+  d |= (uint64_t)1 << 16;
+  d |= (uint64_t)(512 >> 4) << 32;
+  d |= (uint64_t)1 << 46;
+  d |= (uint64_t)4 << 61;            // SWIZZLE_64B
   return d;
 }
 // Instruction descriptor kind::f16: D=f32 (bit 4), A/B format 0 = f16 (1 would be bf16), both K-major, M=128.
