@@ -158,11 +158,6 @@ __device__ __forceinline__ void epi_convert32(const uint32_t (&v)[64], int c0, u
   }
 }
 
-__device__ __forceinline__ bool elect_one() {
-  uint32_t pred;
-  asm volatile("{\n.reg .pred p;\nelect.sync _|p, 0xffffffff;\nselp.u32 %0, 1, 0, p;\n}" : "=r"(pred));
-  return pred != 0;
-}
 
 __device__ long long g_fwd_dbg[8];  // NB_FWD_DEBUG & 16: cycles the MMA issuer of CTA 0 spent per wait kind
 

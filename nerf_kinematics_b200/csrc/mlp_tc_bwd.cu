@@ -79,6 +79,11 @@ __global__ void pack_weights_t_kernel(const float* __restrict__ params, const Pa
 }
 
 // ------------------------------------------------------------------------------------ dgrad chain
+// flags of the dgrad MMA issuer's step program (bits 0-1: gradient block to wait for)
+enum : uint32_t { BF_WAIT_ACT = 4u, BF_K1 = 8u, BF_ACC = 16u, BF_LAST = 32u, BF_BUF1 = 64u };
+// constant upper half of a SWIZZLE_128B K-major operand descriptor (see umma_desc)
+constexpr uint64_t kDescHi128 = ((uint64_t)1 << 16) | ((uint64_t)(1024 >> 4) << 32) | ((uint64_t)1 << 46) | ((uint64_t)2 << 61);
+
 struct BwArgs {
   const unsigned char* wt;
   const float* d_raw;             // [n_points, 4]
@@ -106,10 +111,33 @@ mlp_tc_dgrad_kernel(const __grid_constant__ BwPlan plan, const BwArgs a) {
   uint64_t* bar_act = bar_draw + 1;
   uint64_t* bar_acc = bar_act + 4;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bar_acc + 2);
+  uint4* prog = reinterpret_cast<uint4*>(reinterpret_cast<unsigned char*>(tmem_slot) + 16 + ((16 - (smem_u32(tmem_slot) & 15u)) & 15u));
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const long long n_tiles = (a.n_points + kTileM - 1) / kTileM;
 
+  if (threadIdx.x == 192) {
+    // MMA issuer step program, one entry per K-block: x = byte offset of the A operand block from the gradient
+    // tiles' base (the d_raw tile follows them), y = instruction descriptor, z = flags, w = dZ-record block the
+    // awaited gradient block is saved to
+    int i = 0;
+    for (int s = 0; s < plan.n_stages; ++s) {
+      const BwStage& st = plan.st[s];
+      for (int kb = 0; kb < st.n_kb; ++kb) {
+        const int sidx = st.a_src[kb];
+        uint4 e;
+        e.x = (uint32_t)((sidx < 4 ? sidx : a.n_g_blocks) * kBlockBytes);
+        e.y = umma_idesc(st.n_main);
+        e.z = (s & 1) ? BF_BUF1 : 0u;
+        e.w = 0u;
+        if (sidx < 4) { e.z |= BF_WAIT_ACT | (uint32_t)sidx; e.w = (uint32_t)(plan.st[s - 1].drec_blk + sidx); }
+        if (st.k_steps[kb] == 1) e.z |= BF_K1;
+        if (kb != 0) e.z |= BF_ACC;
+        if (kb == st.n_kb - 1) e.z |= BF_LAST;
+        prog[i++] = e;
+      }
+    }
+  }
   if (threadIdx.x == 0) {
     for (int i = 0; i < kRing; ++i) {
       mbar_init(smem_u32(w_full + i), 1);
@@ -175,57 +203,74 @@ mlp_tc_dgrad_kernel(const __grid_constant__ BwPlan plan, const BwArgs a) {
     }
   } else if (warp == 1) {
     // ============================ MMA issuer ============================
-    if (lane == 0) {
-      uint32_t slot = 0, phase = 0, draw_phase = 0;
-      uint32_t act_phase[4] = {0, 0, 0, 0};
-      for (long long tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
-        unsigned char* dt = a.drec + (size_t)tile * plan.drec_blocks * kBlockBytes;
-        mbar_wait(smem_u32(bar_draw), draw_phase);
-        draw_phase ^= 1;
-        tc_fence_after();
-        bulk_s2g(dt + (size_t)plan.draw_blk * kBlockBytes, smem_u32(draw), kBlockBytes);
+    // Whole warp, warp-uniform control flow over a step program in shared memory (one entry per K-block); only the
+    // tcgen05 / bulk-copy instructions are predicated on one elected lane (see mlp_tc.cu: the issue loop must stay
+    // well below the tensor time of a step or the pipe starves).
+    uint32_t slot = 0, phase = 0, draw_phase = 0, ph_act = 0;
+    const uint32_t gact_s = smem_u32(gact), ring_s = smem_u32(ring), draw_s = smem_u32(draw);
+    const uint32_t w_full_s = smem_u32(w_full), w_empty_s = smem_u32(w_empty), bar_act_s = smem_u32(bar_act);
+    const uint32_t bar_acc_s = smem_u32(bar_acc);
+    const int n_steps = plan.n_steps;
+    const BwStage& last = plan.st[plan.n_stages - 1];
+    for (long long tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+      unsigned char* dt = a.drec + (size_t)tile * plan.drec_blocks * kBlockBytes;
+      mbar_wait(smem_u32(bar_draw), draw_phase);
+      draw_phase ^= 1;
+      tc_fence_after();
+      if (elect_one()) {
+        bulk_s2g(dt + (size_t)plan.draw_blk * kBlockBytes, draw_s, kBlockBytes);
         bulk_commit();
-        for (int s = 0; s < plan.n_stages; ++s) {
-          const BwStage& st = plan.st[s];
-          const int buf = s & 1;
-          const uint32_t d_main = tmem_base + buf * 256;
-          const uint32_t idesc = umma_idesc(st.n_main);
-          for (int kb = 0; kb < st.n_kb; ++kb) {
-            const int sidx = st.a_src[kb];
-            uint32_t a_base;
-            if (sidx < 4) {
-              mbar_wait(smem_u32(bar_act + sidx), act_phase[sidx]);
-              act_phase[sidx] ^= 1;
-              tc_fence_after();
-              a_base = smem_u32(gact + sidx * kBlockBytes);
-              bulk_s2g(dt + (size_t)(plan.st[s - 1].drec_blk + sidx) * kBlockBytes, a_base, kBlockBytes);
-              bulk_commit();
-            } else {
-              a_base = smem_u32(draw);
-            }
-            mbar_wait(smem_u32(w_full + slot), phase);
-            tc_fence_after();
-            const uint32_t b_base = smem_u32(ring + slot * plan.ring_stage_bytes);
-            const int ks = st.k_steps[kb];
-            for (int k = 0; k < ks; ++k)
-              tc_mma(d_main, umma_desc(a_base + k * 32), umma_desc(b_base + k * 32), idesc, (kb | k) != 0 ? 1u : 0u);
-            tc_commit(smem_u32(w_empty + slot));
-            if (++slot == kRing) { slot = 0; phase ^= 1; }
+      }
+      __syncwarp();
+      uint4 e = prog[0];
+      for (int i = 0; i < n_steps; ++i) {
+        const uint4 en = prog[i + 1 < n_steps ? i + 1 : i];  // prefetch
+        const uint32_t fl = e.z;
+        if (fl & BF_WAIT_ACT) {
+          const uint32_t j = fl & 3u;
+          mbar_wait(bar_act_s + 8 * j, (ph_act >> j) & 1u);
+          ph_act ^= 1u << j;
+          if (elect_one()) {
+            bulk_s2g(dt + (size_t)e.w * kBlockBytes, gact_s + e.x, kBlockBytes);
+            bulk_commit();
           }
-          bulk_wait_read0();  // record stores have read the tiles this stage's epilogue overwrites
-          tc_commit(smem_u32(bar_acc + buf));
+          __syncwarp();
         }
-        // the last stage's gradient tiles feed no MMA; they only go to the record
-        const BwStage& last = plan.st[plan.n_stages - 1];
-        for (int j = 0; j < last.n_out; ++j) {
-          mbar_wait(smem_u32(bar_act + j), act_phase[j]);
-          act_phase[j] ^= 1;
-          bulk_s2g(dt + (size_t)(last.drec_blk + j) * kBlockBytes, smem_u32(gact + j * kBlockBytes), kBlockBytes);
+        mbar_wait(w_full_s + 8 * slot, phase);
+        tc_fence_after();
+        const uint64_t a_desc = kDescHi128 | (uint64_t)(((gact_s + e.x) & 0x3FFFFu) >> 4);
+        const uint64_t b_desc = kDescHi128 | (uint64_t)(((ring_s + slot * plan.ring_stage_bytes) & 0x3FFFFu) >> 4);
+        const uint32_t d_main = tmem_base + ((fl & BF_BUF1) ? 256u : 0u);
+        if (elect_one()) {
+          tc_mma(d_main, a_desc, b_desc, e.y, (fl & BF_ACC) ? 1u : 0u);
+          if (!(fl & BF_K1)) {
+            tc_mma(d_main, a_desc + 2, b_desc + 2, e.y, 1u);
+            tc_mma(d_main, a_desc + 4, b_desc + 4, e.y, 1u);
+            tc_mma(d_main, a_desc + 6, b_desc + 6, e.y, 1u);
+          }
+          tc_commit(w_empty_s + 8 * slot);
+          if (fl & BF_LAST) {
+            bulk_wait_read0();  // record stores have read the tiles this stage's epilogue overwrites
+            tc_commit(bar_acc_s + ((fl & BF_BUF1) ? 8u : 0u));
+          }
+        }
+        __syncwarp();
+        if (++slot == kRing) { slot = 0; phase ^= 1; }
+        e = en;
+      }
+      // the last stage's gradient tiles feed no MMA; they only go to the record
+      for (int j = 0; j < last.n_out; ++j) {
+        mbar_wait(bar_act_s + 8 * j, (ph_act >> j) & 1u);
+        ph_act ^= 1u << j;
+        if (elect_one()) {
+          bulk_s2g(dt + (size_t)(last.drec_blk + j) * kBlockBytes, gact_s + j * kBlockBytes, kBlockBytes);
           bulk_commit();
         }
+        __syncwarp();
       }
-      bulk_wait0();
     }
+    if (elect_one()) bulk_wait0();
+    __syncwarp();
   } else {
     // ============================ epilogue warps (thread == row) ============================
     const int q = warp & 3;
@@ -639,6 +684,8 @@ bool bw_build_plan(const Graph& g, PackedBf16* p, std::vector<PackSegT>& segs, c
   for (int s = 0; s < bw.n_stages; ++s)
     if (bw.st[s].n_kb > kMaxKB) { *why = "too many K blocks"; return false; }
   bw.ring_stage_bytes = (int)round_up(ring_max, 1024);
+  bw.n_steps = 0;
+  for (int s = 0; s < bw.n_stages; ++s) bw.n_steps += bw.st[s].n_kb;
   bw.draw_blk = bw.drec_blocks++;
   p->wt_bytes = woff;
 
@@ -693,6 +740,7 @@ static size_t bw_smem_bytes(const BwPlan& bw, int n_g_blocks) {
   b += (size_t)(n_g_blocks + 1 + kMaskRing) * kBlockBytes;
   b += (size_t)kRing * bw.ring_stage_bytes;
   b += (2 * kRing + 2 * kMaskRing + 1 + 4 + 2) * sizeof(uint64_t) + 16;
+  b += 32 + (size_t)bw.n_steps * sizeof(uint4);
   return b;
 }
 static size_t wg_smem_bytes() { return 1024 + (size_t)216 * 1024 + (2 * kWgMaxStages + 1) * 8 + 16; }

@@ -60,6 +60,7 @@ struct BwStage {
 };
 struct BwPlan {
   int n_stages, drec_blocks, ring_stage_bytes;
+  int n_steps;          // K-blocks per tile over all stages (entries of the MMA issuer's step program)
   int draw_blk;         // dZ-record block of the scaled 16-bit d_raw tile (operand of the head wgrad units)
   BwStage st[kMaxStages];
 };
@@ -184,6 +185,13 @@ __device__ __forceinline__ void tc_mma(uint32_t d_tmem, uint64_t a_desc, uint64_
       "}\n" ::"r"(d_tmem),
       "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(acc)
       : "memory");
+}
+// One lane of a converged warp (warp-uniform issue loops predicate their tcgen05 / bulk-copy instructions on it, so
+// descriptors and loop state stay in uniform registers).
+__device__ __forceinline__ bool elect_one() {
+  uint32_t pred;
+  asm volatile("{\n.reg .pred p;\nelect.sync _|p, 0xffffffff;\nselp.u32 %0, 1, 0, p;\n}" : "=r"(pred));
+  return pred != 0;
 }
 __device__ __forceinline__ void tc_wait_ld() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
 
