@@ -16,6 +16,7 @@ Two B200-side additions over the reference loop, both optional:
     small device array refreshed before each replay.
 """
 import ctypes as C
+import os
 import math
 
 import torch
@@ -70,6 +71,10 @@ class TrainStep:
         self._ws = None
         self._ws_cache = {}
         self._graphs = {}
+        # world > 1: the all-reduce runs eagerly between two captured halves (forward+backward | Adam).  Capturing the
+        # NCCL collective itself (NB_SPLIT_GRAPH=0) measured the same step time on 2 B200 but left the process group
+        # unable to shut down cleanly.
+        self._split_graph = bool(int(os.environ.get("NB_SPLIT_GRAPH", "1")))
         self.launches_per_step = None  # kernels inside one captured iteration (graph mode)
         self.graph_replays = 0
         if self.fused:
@@ -222,13 +227,33 @@ class TrainStep:
         # run the forward/backward once without touching parameters or moments
         self.forward_backward(s_rays, s_tgt, force_pack=True, zero_bucket=False)
         self.bucket.zero_()
+        # NCCL creates its communicator (allocations, host syncs) on the first collective: that cannot happen inside a
+        # capture, so run one all-reduce of the zeroed bucket eagerly first
+        self.allreduce()
         torch.cuda.synchronize(self.dev)
-        graph = torch.cuda.CUDAGraph()
         before = ops.launch_count()
-        with torch.cuda.graph(graph):
-            self._device_iteration(s_rays, s_tgt)
+        g = None
+        if self.world == 1 or not self._split_graph:
+            try:
+                graph = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(graph):
+                    self._device_iteration(s_rays, s_tgt)
+                g = (graph, None, s_rays, s_tgt)
+            except Exception:  # collective not capturable on this stack: capture the two local halves instead
+                if self.world == 1:
+                    raise
+                self._split_graph = True
+                torch.cuda.synchronize(self.dev)
+                self.bucket.zero_()
+                before = ops.launch_count()
+        if g is None:
+            ga, gb = torch.cuda.CUDAGraph(), torch.cuda.CUDAGraph()
+            with torch.cuda.graph(ga):
+                self.forward_backward(s_rays, s_tgt, force_pack=True, zero_bucket=False)
+            with torch.cuda.graph(gb):
+                self._fused_adam()
+            g = (ga, gb, s_rays, s_tgt)
         self.launches_per_step = ops.launch_count() - before
-        g = (graph, s_rays, s_tgt)
         self._graphs[key] = g
         return g
 
@@ -240,10 +265,13 @@ class TrainStep:
         self._set_hyper()
         if self.use_graph and rnd is None:
             rays, target = _f32(rays, "rays"), _f32(target, "target")
-            graph, s_rays, s_tgt = self._graph_for(rays, target)
+            graph, graph_opt, s_rays, s_tgt = self._graph_for(rays, target)
             s_rays.copy_(rays, non_blocking=True)
             s_tgt.copy_(target, non_blocking=True)
             graph.replay()
+            if graph_opt is not None:  # split mode: the all-reduce runs eagerly between the two captured halves
+                self.allreduce()
+                graph_opt.replay()
             self.graph_replays += 1
             loss = self.loss_buf
         else:
