@@ -68,3 +68,20 @@ def test_bf16_tensor_core_path_against_fp32_oracle():
         err = maxdiff(got, ref)
         scale = float(ref.abs().max())
         assert err <= 2e-2 * max(1.0, scale), (kind, err, scale)
+
+
+@pytest.mark.parametrize("n_points", [77, 128 * 3 + 5, 128 * 333 + 1])
+def test_bf16_pair_kernel_ragged_tile_counts(n_points):
+    """The forward kernel takes 128-point tiles two at a time from a per-CTA contiguous range: cover a lone partial
+    tile, an even split and ranges with a trailing single tile (odd tiles per CTA), for both graphs."""
+    g = torch.Generator().manual_seed(n_points)
+    pts = (torch.rand(n_points, 1, 3, generator=g) * 2 - 1) * 3.0
+    dirs = torch.nn.functional.normalize(torch.randn(n_points, 3, generator=g), dim=-1)
+    for kind, sd in (("tf", O.init_tf8x256_state(seed=2)), ("flexible", O.init_flexible_state(seed=3))):
+        ref = O.run_mlp(kind, sd, pts, dirs, 10, 4)
+        m = nk.model_from_state_dict(sd).to(DEV)
+        m.precision = "bf16"
+        got = m.query(pts.to(DEV), dirs.to(DEV))
+        assert torch.isfinite(got).all()
+        err = maxdiff(got, ref)
+        assert err <= 2e-2 * max(1.0, float(ref.abs().max())), (kind, n_points, err)
