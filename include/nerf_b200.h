@@ -86,6 +86,12 @@ int nb_model_pack(nb_model_t* m, int precision, nb_stream_t stream);
 /* FLOPs (2*MAC, unpadded) of one forward evaluation of one point: SURVEY 8d "algorithmic flops". */
 int64_t nb_model_flops_per_point(const nb_model_t* m);
 
+/* output stage of render_path (TF run_nerf.py:358-373, to8b run_nerf_helpers.py:17 =
+ * (255 * clip(x, 0, 1)).astype(uint8), i.e. truncation) and the PSNR it prints against gt_imgs
+ * (-10 * log10(mean((rgb - gt)^2))): `mse_accum` (device, 1 double, caller-zeroed) receives sum((x - gt)^2) when gt
+ * is given; out8 may be null.  n = number of scalars. */
+int nb_to8b(const float* x, const float* gt, int64_t n, unsigned char* out8, double* mse_accum, nb_stream_t stream);
+
 /* ---------------------------------------------------------------- a1 ray generation
  * Replaces get_rays (TF run_nerf_helpers.py:123-130) / get_ray_bundle (PT nerf_helpers.py:67-110).
  * dir_cam = [(col-cx)/fx, -(row-cy)/fy, -1]; rays_d = sum_j dir_cam[j]*c2w[k][j]; rays_o = c2w[:,3].
@@ -94,6 +100,13 @@ int64_t nb_model_flops_per_point(const nb_model_t* m);
  */
 int nb_get_rays(int H, int W, float fx, float fy, float cx, float cy, const float* c2w34_host, int row0, int row1,
                 float* rays_o, float* rays_d, nb_stream_t stream);
+
+/* rays of selected pixels only.  The training loops draw N_rand pixel indices per step and build
+ * the whole image's bundle to keep them (TF run_nerf.py:762-774 `coords[select_inds]`, PT train_nerf.py:240-253);
+ * this generates just those rays.  pixel_index: DEVICE int64 [n], row-major index row*W + col (the order of
+ * `reshape(-1, 3)` on the [H, W, 3] bundle).  Bit-identical to gathering nb_get_rays' output. */
+int nb_get_rays_at(int H, int W, float fx, float fy, float cx, float cy, const float* c2w34_host,
+                   const int64_t* pixel_index, int64_t n, float* rays_o, float* rays_d, nb_stream_t stream);
 
 /* a3: ndc_rays (TF run_nerf_helpers.py:143-178 == PT nerf_helpers.py:170-197). In-place allowed.
  * focal / near are doubles because the reference evaluates -1/(W/(2*focal)) with Python (double) scalars

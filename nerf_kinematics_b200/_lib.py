@@ -55,6 +55,8 @@ SIGNATURES = {
     "nb_model_pack": (i32, [p, i32, p]),
     "nb_model_flops_per_point": (i64, [p]),
     "nb_get_rays": (i32, [i32, i32, f32, f32, f32, f32, C.POINTER(f32), i32, i32, p, p, p]),
+    "nb_get_rays_at": (i32, [i32, i32, f32, f32, f32, f32, C.POINTER(f32), p, i64, p, p, p]),
+    "nb_to8b": (i32, [p, p, i64, p, p, p]),
     "nb_ndc_rays": (i32, [i32, i32, f64, f64, p, p, i64, p, p, p]),
     "nb_make_ray_batch": (i32, [p, p, p, i64, i32, i32, i32, i32, f64, f64, f64, p, p, p, p]),
     "nb_sample_coarse": (i32, [p, i32, i64, i32, i32, p, p, p]),

@@ -4,6 +4,8 @@
 // coordinate by up to 2^9, so contraction is disabled for the whole file (all kernels here are
 // bandwidth-bound, FMA would buy nothing).
 #include <math.h>
+
+#include <algorithm>
 #include <stdarg.h>
 
 #include "common.cuh"
@@ -38,20 +40,76 @@ struct Cam {
 };
 
 // ------------------------------------------------------------------------------------ a1
-__global__ void get_rays_kernel(int W, float fx, float fy, float cx, float cy, Cam cam, int row0, int64_t n,
-                                float* __restrict__ ro, float* __restrict__ rd) {
-  int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (idx >= n) return;
-  int col = (int)(idx % W);
-  int row = row0 + (int)(idx / W);
-  float dx = ((float)col - cx) / fx;
-  float dy = -(((float)row - cy) / fy);
-  float dz = -1.0f;
+// get_rays (nerf/run_nerf_helpers.py:123-130 == get_ray_bundle, nerf-pytorch/nerf/nerf_helpers.py:67-110):
+// dir_cam = [(col - cx)/fx, -(row - cy)/fy, -1]; rays_d[k] = sum_j dir_cam[j] * R[k][j] (multiply, then sum over the
+// last axis in this association); rays_o = c2w[:3, 3].  True IEEE divisions, no +0.5 pixel centre.
+__device__ __forceinline__ void pixel_ray(int col, int row, float fx, float fy, float cx, float cy, const Cam& cam,
+                                          float d[3]) {
+  const float dx = ((float)col - cx) / fx;
+  const float dy = -(((float)row - cy) / fy);
+  const float dz = -1.0f;
+#pragma unroll
+  for (int k = 0; k < 3; ++k) d[k] = (dx * cam.r[4 * k + 0] + dy * cam.r[4 * k + 1]) + dz * cam.r[4 * k + 2];
+}
+
+// grid = (ceil(W / 256), rows): a block owns up to 256 consecutive pixels of one row, stages their 768 floats in shared
+// memory and writes them back as fully coalesced 128-byte warp stores (no 64-bit index division, no strided stores).
+__global__ void __launch_bounds__(256)
+get_rays_kernel(int W, float fx, float fy, float cx, float cy, Cam cam, int row0, float* __restrict__ ro,
+                float* __restrict__ rd) {
+  __shared__ float sd[768];
+  const int col0 = blockIdx.x * 256, col = col0 + threadIdx.x;
+  const int row = row0 + blockIdx.y;
+  const int npix = min(256, W - col0);
+  if (col < W) {
+    float d[3];
+    pixel_ray(col, row, fx, fy, cx, cy, cam, d);
+    sd[3 * threadIdx.x + 0] = d[0];
+    sd[3 * threadIdx.x + 1] = d[1];
+    sd[3 * threadIdx.x + 2] = d[2];
+  }
+  __syncthreads();
+  const int64_t base = ((int64_t)blockIdx.y * W + col0) * 3;
+  for (int i = threadIdx.x; i < 3 * npix; i += 256) {
+    rd[base + i] = sd[i];
+    const int k = i % 3;
+    ro[base + i] = cam.r[4 * k + 3];
+  }
+}
+
+// rays of selected pixels only (the training loop draws N_rand pixel indices per step and the
+// reference generates the whole image's rays to keep 1 024 of them, nerf-pytorch/train_nerf.py:240-253).
+__global__ void get_rays_at_kernel(int W, float fx, float fy, float cx, float cy, Cam cam, const int64_t* __restrict__ pix,
+                                   int64_t n, float* __restrict__ ro, float* __restrict__ rd) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const int64_t p = pix[i];
+  const int row = (int)(p / W), col = (int)(p - (int64_t)row * W);
+  float d[3];
+  pixel_ray(col, row, fx, fy, cx, cy, cam, d);
 #pragma unroll
   for (int k = 0; k < 3; ++k) {
-    float v = (dx * cam.r[4 * k + 0] + dy * cam.r[4 * k + 1]) + dz * cam.r[4 * k + 2];
-    rd[idx * 3 + k] = v;
-    ro[idx * 3 + k] = cam.r[4 * k + 3];
+    rd[i * 3 + k] = d[k];
+    ro[i * 3 + k] = cam.r[4 * k + 3];
+  }
+}
+
+// ------------------------------------------------------------------------------------ f3: to8b + squared error
+__global__ void to8b_kernel(const float* __restrict__ x, const float* __restrict__ gt, int64_t n,
+                            unsigned char* __restrict__ out8, double* __restrict__ mse_accum) {
+  double local = 0.0;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    const float v = x[i];
+    if (out8 != nullptr) out8[i] = (unsigned char)(255.0f * fminf(fmaxf(v, 0.0f), 1.0f));  // numpy astype(uint8): truncation
+    if (gt != nullptr) {
+      const float d = v - gt[i];
+      local += (double)(d * d);
+    }
+  }
+  if (gt != nullptr && mse_accum != nullptr) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) local += __shfl_xor_sync(0xffffffffu, local, o);
+    if ((threadIdx.x & 31) == 0) atomicAdd(mse_accum, local);
   }
 }
 
@@ -210,7 +268,33 @@ int nb_get_rays(int H, int W, float fx, float fy, float cx, float cy, const floa
   NB_REQUIRE(rays_o && rays_d, "nb_get_rays: null output");
   Cam cam;
   memcpy(cam.r, c2w, sizeof(cam.r));
-  get_rays_kernel<<<(unsigned)ceil_div(n, 256), 256, 0, as_stream(stream)>>>(W, fx, fy, cx, cy, cam, row0, n, rays_o, rays_d);
+  NB_REQUIRE(row1 - row0 <= 65535, "nb_get_rays: more than 65535 rows in one call");
+  dim3 grid((unsigned)ceil_div(W, 256), (unsigned)(row1 - row0));
+  get_rays_kernel<<<grid, 256, 0, as_stream(stream)>>>(W, fx, fy, cx, cy, cam, row0, rays_o, rays_d);
+  NB_LAUNCHED();
+  return NB_OK;
+}
+
+int nb_to8b(const float* x, const float* gt, int64_t n, unsigned char* out8, double* mse_accum, nb_stream_t stream) {
+  NB_REQUIRE(n >= 0, "nb_to8b: negative size");
+  if (n == 0) return NB_OK;
+  NB_REQUIRE(x && (out8 || gt), "nb_to8b: null pointer");
+  NB_REQUIRE(gt == nullptr || mse_accum != nullptr, "nb_to8b: gt given without an accumulator");
+  const unsigned grid = (unsigned)std::min<int64_t>(ceil_div(n, 256), (int64_t)sm_count() * 8);
+  to8b_kernel<<<grid, 256, 0, as_stream(stream)>>>(x, gt, n, out8, mse_accum);
+  NB_LAUNCHED();
+  return NB_OK;
+}
+
+int nb_get_rays_at(int H, int W, float fx, float fy, float cx, float cy, const float* c2w, const int64_t* pixel_index,
+                   int64_t n, float* rays_o, float* rays_d, nb_stream_t stream) {
+  NB_REQUIRE(H > 0 && W > 0 && c2w && n >= 0, "nb_get_rays_at: bad arguments");
+  if (n == 0) return NB_OK;
+  NB_REQUIRE(pixel_index && rays_o && rays_d, "nb_get_rays_at: null pointer");
+  Cam cam;
+  memcpy(cam.r, c2w, sizeof(cam.r));
+  get_rays_at_kernel<<<(unsigned)ceil_div(n, 256), 256, 0, as_stream(stream)>>>(W, fx, fy, cx, cy, cam, pixel_index, n, rays_o,
+                                                                           rays_d);
   NB_LAUNCHED();
   return NB_OK;
 }

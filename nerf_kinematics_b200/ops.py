@@ -53,6 +53,44 @@ def get_rays(H: int, W: int, K, c2w, row0: int = 0, row1: int = None, device=Non
     return ro, rd
 
 
+def get_rays_at(H: int, W: int, K, c2w, pixel_index, device=None):
+    """Rays of the selected pixels only: pixel_index int64 [n] = row * W + col.  Bit-identical to
+    `get_rays(H, W, K, c2w)` flattened with reshape(-1, 3) and indexed (train_nerf.py:240-253)."""
+    _lib.require_cuda()
+    fx, fy, cx, cy = intrinsics(H, W, K)
+    c2w_h = torch.as_tensor(c2w, dtype=torch.float32).detach().cpu()[:3, :4].contiguous()
+    if device is None:
+        device = pixel_index.device if isinstance(pixel_index, torch.Tensor) and pixel_index.is_cuda else torch.device("cuda")
+    idx = torch.as_tensor(pixel_index, dtype=torch.int64).to(device).contiguous()
+    with torch.cuda.device(device):
+        ro = torch.empty((idx.numel(), 3), dtype=torch.float32, device=device)
+        rd = torch.empty_like(ro)
+        arr = (C.c_float * 12)(*c2w_h.reshape(-1).tolist())
+        check(lib().nb_get_rays_at(H, W, fx, fy, cx, cy, arr, _ptr(idx), idx.numel(), _ptr(ro), _ptr(rd), _stream()),
+              "nb_get_rays_at")
+    return ro, rd
+
+
+def to8b_psnr(x, gt=None, want_u8=True):
+    """render_path's output stage on the device: uint8 image (255 * clip(x, 0, 1), truncated like
+    numpy astype) and, against `gt`, the PSNR the reference prints (run_nerf.py:364-366).  Returns (u8 or None, psnr or None)."""
+    _lib.require_cuda()
+    x = _f32(x, "x")
+    out8 = torch.empty(x.shape, dtype=torch.uint8, device=x.device) if want_u8 else None
+    acc = None
+    if gt is not None:
+        gt = _f32(gt.to(x.device), "gt")
+        if gt.shape != x.shape:
+            raise ValueError("to8b_psnr: gt shape %s != image shape %s" % (tuple(gt.shape), tuple(x.shape)))
+        acc = torch.zeros((1,), dtype=torch.float64, device=x.device)
+    with torch.cuda.device(x.device):
+        check(lib().nb_to8b(_ptr(x), _optptr(gt), x.numel(), _optptr(out8), _optptr(acc), _stream()), "nb_to8b")
+    psnr = None
+    if acc is not None:
+        psnr = -10.0 * torch.log10(acc / x.numel()).to(torch.float32)
+    return out8, psnr
+
+
 def intrinsics(H, W, K):
     """(fx, fy, cx, cy) from a 3x3 K or a scalar focal (then cx = W/2, cy = H/2 like the reference)."""
     if isinstance(K, torch.Tensor) and K.numel() == 1:

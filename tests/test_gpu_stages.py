@@ -207,3 +207,39 @@ def test_mse_loss():
     loss, d = ops.mse_loss(a.to(DEV), b.to(DEV))
     assert abs(float(loss) - float(torch.nn.functional.mse_loss(a, b))) <= 1e-6
     assert maxdiff(d, 2 * (a - b) / a.numel()) <= 1e-9
+
+
+def test_get_rays_wide_rows_and_selected_pixels():
+    """Images wider than one 256-pixel block with a ragged last block (1280x720 wheel frame, 504x378 fern), and the
+    device-side ray selection of SURVEY 8(f) f1: bit-identical to gathering the full bundle."""
+    c2w = O.pose_spherical(17.0, -30.0, 4.0)
+    for (H, W, K) in ((72, 1280, torch.tensor([[674.419, 0, 640.0], [0, 649.457, 36.0], [0, 0, 1]])), (38, 504, 407.57)):
+        f = K if not isinstance(K, torch.Tensor) else None
+        o, d = ops.get_rays(H, W, K, c2w)
+        if f is not None:
+            ro, rd = O.pixel_rays(H, W, f, c2w)
+            assert maxdiff(d, rd) <= 1e-6 and maxdiff(o, ro) == 0
+        else:  # K-API: columns / rows independent -> check against the closed form in fp64
+            jj, ii = torch.meshgrid(torch.arange(H, dtype=torch.float64), torch.arange(W, dtype=torch.float64), indexing="ij")
+            dirs = torch.stack([(ii - 640.0) / 674.419, -(jj - 36.0) / 649.457, -torch.ones_like(ii)], -1)
+            ref = (dirs[..., None, :] * torch.as_tensor(c2w, dtype=torch.float64)[:3, :3]).sum(-1)
+            assert maxdiff(d.double(), ref) <= 1e-6
+        o2, d2 = ops.get_rays(H, W, K, c2w, row0=3, row1=H - 2)
+        assert torch.equal(d2, d[3:H - 2]) and torch.equal(o2, o[3:H - 2])
+        sel = torch.from_numpy(np.random.RandomState(0).choice(H * W, 1024, replace=False)).to(DEV)
+        o3, d3 = ops.get_rays_at(H, W, K, c2w, sel)
+        assert torch.equal(d3, d.reshape(-1, 3)[sel]) and torch.equal(o3, o.reshape(-1, 3)[sel])
+
+
+def test_to8b_and_psnr_output_stage():
+    """render_path's output stage (run_nerf.py:358-373): to8b truncates like numpy astype(uint8); PSNR vs gt."""
+    g = torch.Generator().manual_seed(5)
+    img = (torch.rand(37, 53, 3, generator=g) * 1.4 - 0.2)
+    gt = torch.rand(37, 53, 3, generator=g)
+    u8, psnr = ops.to8b_psnr(img.to(DEV), gt.to(DEV))
+    ref8 = (255 * np.clip(img.numpy(), 0, 1)).astype(np.uint8)
+    assert np.array_equal(u8.cpu().numpy(), ref8)
+    ref_psnr = -10.0 * np.log10(np.mean(np.square(img.numpy() - gt.numpy())))
+    assert abs(float(psnr) - ref_psnr) <= 1e-4
+    u8b, none = ops.to8b_psnr(img.to(DEV))
+    assert none is None and torch.equal(u8b, u8)
