@@ -95,22 +95,46 @@ def render_path(render_poses, hwf, chunk, render_kwargs, gt_imgs=None, savedir=N
     if render_factor != 0:
         H, W = H // render_factor, W // render_factor
         focal = focal / render_factor if not hasattr(focal, "shape") or np.ndim(focal) == 0 else _scale_K(focal, render_factor)
-    rgbs, disps = [], []
+    # the reference converts every frame with .numpy() as soon as it is rendered (run_nerf.py:358),
+    # which serialises host and device.  Here each frame is copied into pinned host memory asynchronously (the next
+    # pose renders while the previous one drains), to8b / PSNR run on the device, and the host waits once at the end.
+    poses_list = [torch.as_tensor(c)[:3, :4] for c in render_poses]
+    M = len(poses_list)
+    rgbs_h = disps_h = u8_h = None
+    psnrs = []
     t = time.time()
     with torch.no_grad():
-        for i, c2w in enumerate(render_poses):
+        for i, c2w in enumerate(poses_list):
             if verbose:
                 print(i, time.time() - t)
                 t = time.time()
-            c2w = torch.as_tensor(c2w)[:3, :4]
             rgb, disp, acc, _ = render(H, W, focal, chunk=chunk, c2w=c2w, **render_kwargs)
-            rgbs.append(rgb.cpu().numpy())
-            disps.append(disp.cpu().numpy())
-            if gt_imgs is not None and render_factor == 0 and verbose:
-                print(-10.0 * np.log10(np.mean(np.square(rgbs[-1] - np.asarray(gt_imgs[i])))))
-            if savedir is not None:
-                _write_png(os.path.join(savedir, "{:03d}.png".format(i)), to8b(rgbs[-1]))
-    return np.stack(rgbs, 0), np.stack(disps, 0)
+            if rgbs_h is None:
+                pin = rgb.is_cuda
+                rgbs_h = torch.empty((M,) + tuple(rgb.shape), dtype=torch.float32, pin_memory=pin)
+                disps_h = torch.empty((M,) + tuple(disp.shape), dtype=torch.float32, pin_memory=pin)
+                if savedir is not None:
+                    u8_h = torch.empty((M,) + tuple(rgb.shape), dtype=torch.uint8, pin_memory=pin)
+            rgbs_h[i].copy_(rgb, non_blocking=True)
+            disps_h[i].copy_(disp, non_blocking=True)
+            want_psnr = gt_imgs is not None and render_factor == 0 and verbose
+            if want_psnr or savedir is not None:
+                gt = torch.as_tensor(np.asarray(gt_imgs[i]), dtype=torch.float32) if want_psnr else None
+                u8, psnr = ops.to8b_psnr(rgb, gt, want_u8=savedir is not None)
+                if u8 is not None:
+                    u8_h[i].copy_(u8, non_blocking=True)
+                if psnr is not None:
+                    psnrs.append(psnr)
+    if rgbs_h is None:
+        return np.zeros((0, H, W, 3), np.float32), np.zeros((0, H, W), np.float32)
+    if torch.cuda.is_available():
+        torch.cuda.synchronize()
+    for p in psnrs:
+        print(float(p))
+    if savedir is not None:
+        for i in range(M):
+            _write_png(os.path.join(savedir, "{:03d}.png".format(i)), u8_h[i].numpy())
+    return rgbs_h.numpy(), disps_h.numpy()
 
 
 def _scale_K(K, factor):

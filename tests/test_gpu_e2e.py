@@ -89,6 +89,16 @@ def test_render_api_tf_semantics_and_chunk_invariance():
         rgbs, disps = nk.render_path([g["c2w"], g["c2w"]], (g["H"], g["W"], g["focal"]), 4096, kw)
     assert rgbs.shape == (2, g["H"], g["W"], 3) and isinstance(rgbs, np.ndarray) and disps.shape == (2, g["H"], g["W"])
     assert maxdiff(torch.from_numpy(rgbs[1]), g["rgb_fine"]) <= 1e-3
+    # output stage: PNGs from the on-device to8b, PSNR against gt_imgs printed like run_nerf.py:364-366
+    import tempfile
+    from PIL import Image
+    with tempfile.TemporaryDirectory() as tmp, torch.no_grad():
+        gt = [g["rgb_fine"].numpy(), g["rgb_fine"].numpy()]
+        rgbs2, _ = nk.render_path([g["c2w"], g["c2w"]], (g["H"], g["W"], g["focal"]), 4096, kw, gt_imgs=gt, savedir=tmp,
+                                  verbose=True)
+        assert np.array_equal(rgbs2, rgbs)
+        png = np.asarray(Image.open(tmp + "/001.png"))
+        assert np.array_equal(png, (255 * np.clip(rgbs[1], 0, 1)).astype(np.uint8))
 
 
 def test_depth_at_the_compositing_boundary():
