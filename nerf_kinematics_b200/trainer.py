@@ -282,6 +282,19 @@ class TrainStep:
             gparam["lr"] = lr
         return loss
 
+    def step_pixels(self, H, W, K, c2w, target_image, pixel_index, near, far, *, ndc=False):
+        """One iteration on selected pixels of one posed image (the loop body of
+        nerf-pytorch/train_nerf.py:240-297 / nerf/run_nerf.py:762-826): only the N_rand selected rays are generated
+        (nb_get_rays_at) instead of the whole image's bundle, targets are gathered on the device.
+        target_image: [H, W, 3] or [H*W, 3] device tensor; pixel_index: int64 [N_rand] = row * W + col."""
+        idx = torch.as_tensor(pixel_index, dtype=torch.int64).to(self.dev)
+        ro, rd = ops.get_rays_at(H, W, K, c2w, idx, device=self.dev)
+        focal = ops.intrinsics(H, W, K)[0]
+        rays = ops.make_ray_batch(ro, rd, near, far, use_viewdirs=bool(self.mc.use_viewdirs), ndc=ndc, H=H, W=W,
+                                  focal=focal)
+        tgt = _f32(target_image, "target_image").reshape(-1, 3)[idx]
+        return self.step(rays, tgt)
+
     def _step_torch_optimizer(self, rays, target, rnd=None):
         """The reference's own optimizer object (any torch.optim) on the parameters' .grad views of the bucket."""
         loss = self.forward_backward(rays, target, rnd)

@@ -376,3 +376,24 @@ def test_cuda_graph_step_equals_eager_step():
         oa = render_chunk(rays, mca, mfa, N_samples=64, N_importance=128, white_bkgd=True, precision="bf16")
         ob = render_chunk(rays, mcb, mfb, N_samples=64, N_importance=128, white_bkgd=True, precision="bf16")
     assert maxdiff(oa["rgb"], ob["rgb"]) <= 1e-4
+
+
+def test_step_pixels_equals_step_on_gathered_rays():
+    """selecting pixels on the device and generating only their rays gives the same iteration as
+    building the whole image's bundle and indexing it (train_nerf.py:240-253)."""
+    import numpy as np
+    from nerf_kinematics_b200 import ops
+    H, W, f = 40, 56, 70.0
+    c2w = O.pose_spherical(25.0, -30.0, 4.0)
+    img = torch.rand(H, W, 3, generator=torch.Generator().manual_seed(3)).to(DEV)
+    sel = torch.from_numpy(np.random.RandomState(1).choice(H * W, 64, replace=False)).to(DEV)
+    a, mca, mfa, _, _ = _train_setup(precision="bf16", cuda_graph=True)
+    b, mcb, mfb, _, _ = _train_setup(precision="bf16", cuda_graph=True)
+    ro, rd = ops.get_rays(H, W, f, c2w)
+    rays = ops.make_ray_batch(ro.reshape(-1, 3)[sel], rd.reshape(-1, 3)[sel], 2.0, 6.0, use_viewdirs=True)
+    for _ in range(2):
+        la = a.step_pixels(H, W, f, c2w, img, sel, 2.0, 6.0).clone()
+        lb = b.step(rays, img.reshape(-1, 3)[sel]).clone()
+        assert torch.equal(la, lb)
+    for (k, pa), (_, pb) in zip(mfa.named_parameters(), mfb.named_parameters()):
+        assert torch.equal(pa, pb), k
