@@ -37,10 +37,8 @@
 namespace nb {
 
 // ------------------------------------------------------------------------------------ weight packing
-__global__ void pack_weights_kernel(const float* __restrict__ params, const PackSeg* __restrict__ segs,
-                                    unsigned char* __restrict__ out) {
-  const PackSeg sg = segs[blockIdx.y];
-  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+__device__ __forceinline__ void pack_weights_body(const float* __restrict__ params, const PackSeg& sg,
+                                                  unsigned char* __restrict__ out, int idx) {
   if (idx >= sg.n_rows * 8) return;
   const int r = idx >> 3, c = idx & 7;
   const int n = sg.row0 + r;
@@ -62,6 +60,11 @@ __global__ void pack_weights_kernel(const float* __restrict__ params, const Pack
                             ((c4 ^ ((n >> 1) & 3)) << 4)) = pk;
 }
 
+__global__ void pack_weights_kernel(const float* __restrict__ params, const PackSeg* __restrict__ segs,
+                                    unsigned char* __restrict__ out) {
+  pack_weights_body(params, segs[blockIdx.y], out, blockIdx.x * blockDim.x + threadIdx.x);
+}
+
 __global__ void pack_bias_kernel(const float* __restrict__ params, const BiasSeg* __restrict__ segs,
                                  float* __restrict__ out) {
   const BiasSeg sg = segs[blockIdx.x];
@@ -69,6 +72,29 @@ __global__ void pack_bias_kernel(const float* __restrict__ params, const BiasSeg
 }
 
 
+
+// One launch for everything a parameter update invalidates: forward image, biases and (train) the transposed image of
+// the dgrad chain.  blockIdx.y walks [forward segments | bias segments | transposed segments].
+__global__ void pack_all_kernel(const float* __restrict__ params, const PackSeg* __restrict__ segs, int n_segs,
+                                unsigned char* __restrict__ out, const BiasSeg* __restrict__ bsegs, int n_bsegs,
+                                float* __restrict__ bias_out, const PackSegT* __restrict__ segs_t, int n_segs_t,
+                                unsigned char* __restrict__ out_t) {
+  int y = blockIdx.y;
+  if (y < n_segs) {
+    pack_weights_body(params, segs[y], out, blockIdx.x * blockDim.x + threadIdx.x);
+    return;
+  }
+  y -= n_segs;
+  if (y < n_bsegs) {
+    if (blockIdx.x == 0) {
+      const BiasSeg sg = bsegs[y];
+      for (int i = threadIdx.x; i < sg.count; i += blockDim.x) bias_out[sg.dst + i] = params[sg.src_off + i];
+    }
+    return;
+  }
+  y -= n_bsegs;
+  if (y < n_segs_t) pack_weights_t_body(params, segs_t[y], out_t, blockIdx.x * blockDim.x + threadIdx.x);
+}
 
 // ------------------------------------------------------------------------------------ point source
 struct TcSrc {
@@ -158,8 +184,6 @@ __device__ __forceinline__ void epi_convert32(const uint32_t (&v)[64], int c0, u
   }
 }
 
-
-__device__ long long g_fwd_dbg[8];  // NB_FWD_DEBUG & 16: cycles the MMA issuer of CTA 0 spent per wait kind
 
 // flags of the MMA issuer's step program
 enum : uint32_t { PF_WAIT_ACT = 4u, PF_WAIT_ENCD = 8u, PF_FIRST = 16u, PF_LAST = 32u, PF_ACC = 64u };
@@ -641,15 +665,13 @@ int packed_build(nb_model* m, cudaStream_t stream) {
     if (rc != NB_OK) return rc;
   }
   PackedBf16* p = m->packed;
-  p->wt_fresh = false;  // the transposed images are rebuilt by the next backward call
-  int max_rows = 0;
-  // one launch over all segments; blockIdx.x covers the largest segment
-  max_rows = 272;
-  dim3 grid((unsigned)ceil_div(max_rows * 8, 256), (unsigned)p->n_segs);
-  pack_weights_kernel<<<grid, 256, 0, stream>>>(m->params, p->d_segs, p->d_w);
+  // forward image + biases + (when the graph trains on tensor cores) the transposed image, in one launch
+  const int n_t = p->bw_supported ? p->n_segs_t : 0;
+  dim3 grid((unsigned)ceil_div(272 * 8, 256), (unsigned)(p->n_segs + p->n_bsegs + n_t));
+  pack_all_kernel<<<grid, 256, 0, stream>>>(m->params, p->d_segs, p->n_segs, p->d_w, p->d_bsegs, p->n_bsegs, p->d_bias,
+                                            p->d_segs_t, n_t, p->d_wt);
   NB_LAUNCHED();
-  pack_bias_kernel<<<p->n_bsegs, 128, 0, stream>>>(m->params, p->d_bsegs, p->d_bias);
-  NB_LAUNCHED();
+  p->wt_fresh = p->bw_supported;
   return NB_OK;
 }
 
@@ -683,18 +705,10 @@ int tc_forward(const nb_model* m, const float* rays, int ray_stride, const float
   TcSrc src{rays, ray_stride, z_vals, n_samples > 0 ? n_samples : 1, pts, viewdirs, points_per_dir > 0 ? points_per_dir : 1};
   const int64_t n_tiles = ceil_div(n_points, kTileM);
   const int grid = (int)std::min<int64_t>(ceil_div(n_tiles, 2), sm_count());
+  // NB_FWD_DEBUG (timing experiments behind the numbers in DESIGN.md, results are then garbage): 1 = producer skips the
+  // weight loads, 2 = epilogue skips the conversion
   static const int dbg = getenv("NB_FWD_DEBUG") ? atoi(getenv("NB_FWD_DEBUG")) : 0;
   mlp_tc_kernel<<<grid, kThreadsTc, p->smem_bytes, stream>>>(p->plan, p->d_w, p->d_bias, src, (long long)n_points, raw, rec, dbg);
-  if (dbg & 16) {
-    long long h[8];
-    cudaDeviceSynchronize();
-    cudaMemcpyFromSymbol(h, g_fwd_dbg, sizeof(h));
-    if (h[4] > 0)
-      fprintf(stderr, "[fwd dbg] pairs %lld: cycles/pair %lld = wait act %lld + wait full %lld + wait drain %lld + issue %lld\n", h[4],
-              h[0] / h[4], h[1] / h[4], h[2] / h[4], h[3] / h[4], (h[0] - h[1] - h[2] - h[3]) / h[4]);
-    memset(h, 0, sizeof(h));
-    cudaMemcpyToSymbol(g_fwd_dbg, h, sizeof(h));
-  }
   NB_LAUNCHED();
   return NB_OK;
 }

@@ -60,22 +60,7 @@ __global__ void absmax_kernel(const float* __restrict__ x, long long n, unsigned
 // ------------------------------------------------------------------------------------ transposed weight packing
 __global__ void pack_weights_t_kernel(const float* __restrict__ params, const PackSegT* __restrict__ segs,
                                       unsigned char* __restrict__ out) {
-  const PackSegT sg = segs[blockIdx.y];
-  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
-  if (idx >= sg.n_rows * 8) return;
-  const int n = idx >> 3, c = idx & 7;
-  float v[8];
-#pragma unroll
-  for (int e = 0; e < 8; ++e) {
-    const int kk = c * 8 + e - sg.kdst0;
-    v[e] = (kk >= 0 && kk < sg.kcount) ? params[sg.src_off + (long long)(sg.krow0 + kk) * sg.ld + sg.col0 + n] : 0.0f;
-  }
-  uint4 pk;
-  pk.x = pack_h2(v[0], v[1], false);
-  pk.y = pack_h2(v[2], v[3], false);
-  pk.z = pack_h2(v[4], v[5], false);
-  pk.w = pack_h2(v[6], v[7], false);
-  *reinterpret_cast<uint4*>(out + sg.dst_off + (long long)n * 128 + ((c ^ (n & 7)) << 4)) = pk;
+  pack_weights_t_body(params, segs[blockIdx.y], out, blockIdx.x * blockDim.x + threadIdx.x);
 }
 
 // ------------------------------------------------------------------------------------ dgrad chain

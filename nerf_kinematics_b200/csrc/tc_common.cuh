@@ -140,6 +140,26 @@ __device__ __forceinline__ uint32_t pack_h2(float lo, float hi, bool relu) {
   return d;
 }
 
+// one 16-byte chunk (8 elements) of a transposed weight chunk for the dgrad chain: chunk row n (layer input), element
+// kdst0+k <- W[krow0+k, col0+n]; SWIZZLE_128B K-major image (used by pack_weights_t_kernel and the combined pack launch)
+__device__ __forceinline__ void pack_weights_t_body(const float* __restrict__ params, const PackSegT& sg,
+                                                    unsigned char* __restrict__ out, int idx) {
+  if (idx >= sg.n_rows * 8) return;
+  const int n = idx >> 3, c = idx & 7;
+  float v[8];
+#pragma unroll
+  for (int e = 0; e < 8; ++e) {
+    const int kk = c * 8 + e - sg.kdst0;
+    v[e] = (kk >= 0 && kk < sg.kcount) ? params[sg.src_off + (long long)(sg.krow0 + kk) * sg.ld + sg.col0 + n] : 0.0f;
+  }
+  uint4 pk;
+  pk.x = pack_h2(v[0], v[1], false);
+  pk.y = pack_h2(v[2], v[3], false);
+  pk.z = pack_h2(v[4], v[5], false);
+  pk.w = pack_h2(v[6], v[7], false);
+  *reinterpret_cast<uint4*>(out + sg.dst_off + (long long)n * 128 + ((c ^ (n & 7)) << 4)) = pk;
+}
+
 // ------------------------------------------------------------------------------------ PTX wrappers
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 
