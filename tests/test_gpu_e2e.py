@@ -218,3 +218,42 @@ def test_bf16_render_within_stated_bound():
     tgt = torch.rand(g["H"], g["W"], 3, generator=torch.Generator().manual_seed(0))
     psnr = lambda im: -10 * torch.log10(torch.mean((im.cpu() - tgt) ** 2))
     assert abs(float(psnr(got[3]) - psnr(g["rgb_fine"]))) <= 0.05
+
+
+def test_render_options_staticcam_render_factor_lindisp():
+    """Option coverage of render / render_path (run_nerf.py:297-307 c2w_staticcam: rays from the static camera, view
+    directions from c2w; :343-347 render_factor; :181-188 lindisp) against the oracle's stage functions."""
+    g = load_golden("e2e_lego")
+    mc, mf = _models("ckpt_lego_lowres3")
+    H, W, f = 20, 24, g["focal"] * 20.0 / g["H"]
+    kw = dict(network_query_fn=None, perturb=0.0, N_importance=128, network_fine=mf, N_samples=64, network_fn=mc,
+              use_viewdirs=True, white_bkgd=True, raw_noise_std=0.0, ndc=False, lindisp=False, near=2.0, far=6.0)
+    cam_a = O.pose_spherical(40.0, -25.0, 4.0)
+    cam_b = g["c2w"]
+    with torch.no_grad():
+        rgb_s, _, acc_s, _ = nk.render(H, W, f, c2w=cam_a[:3, :4], c2w_staticcam=cam_b[:3, :4], **kw)
+        # the same thing spelled out: geometry of camera B, unit view directions of camera A
+        ro_b, rd_b = O.pixel_rays(H, W, f, cam_b)
+        _, rd_a = O.pixel_rays(H, W, f, cam_a)
+        vd = rd_a / rd_a.norm(dim=-1, keepdim=True)
+        rays = torch.cat([ro_b.reshape(-1, 3), rd_b.reshape(-1, 3), torch.full((H * W, 1), 2.0), torch.full((H * W, 1), 6.0),
+                          vd.reshape(-1, 3)], -1)
+        ck = load_golden("ckpt_lego_lowres3")
+        sdc = {k[2:]: v for k, v in ck.items() if k.startswith("c.")}
+        sdf = {k[2:]: v for k, v in ck.items() if k.startswith("f.")}
+        ref = O.render_chunk("flexible", sdc, sdf, rays, n_coarse=64, n_fine=128, n_freq_xyz=mc.n_freq_xyz,
+                             n_freq_dir=mc.n_freq_dir, white_bkgd=True)
+        assert maxdiff(rgb_s.reshape(-1, 3), ref["rgb_fine"]) <= 1e-3
+        # staticcam really changes the result and differs from both plain cameras
+        rgb_b, _, _, _ = nk.render(H, W, f, c2w=cam_b[:3, :4], **kw)
+        assert maxdiff(rgb_s, rgb_b) > 1e-4 and acc_s.shape == (H, W)
+        from nerf_kinematics_b200.render_core import render_chunk
+        out = render_chunk(rays.to(DEV), mc, mf, N_samples=64, N_importance=128, white_bkgd=True)
+        assert maxdiff(out["rgb"].reshape(H, W, 3), rgb_s) <= 1e-4  # rays built on the CPU differ by an ulp
+        # render_factor: H, W and focal divided (run_nerf.py:343-347)
+        rgbs, _ = nk.render_path([cam_b], (2 * H, 2 * W, 2 * f), 4096, kw, render_factor=2)
+        assert rgbs.shape == (1, H, W, 3) and maxdiff(torch.from_numpy(rgbs[0]), rgb_b) == 0
+        # lindisp: coarse depths linear in disparity
+        kw2 = dict(kw, lindisp=True)
+        rgb_l, _, _, ex = nk.render(H, W, f, c2w=cam_b[:3, :4], **kw2)
+        assert torch.isfinite(rgb_l).all() and maxdiff(rgb_l, rgb_b) > 1e-5
