@@ -137,6 +137,20 @@ def run_reference(args):
 
 
 # ------------------------------------------------------------------------------------------ our arm
+def profiled_traffic_bytes():
+    """dram__bytes_read.sum + dram__bytes_write.sum of the roofline kernel's launch (same 32 768-ray x 192-sample
+    workload) from the committed `ncu --set full` capture under profiles/; None if the summary is missing."""
+    try:
+        tot = 0.0
+        for line in open(os.path.join(ROOT, "profiles", "r1b_mlp_tc_pair_kernel_ncu_full.csv")):
+            parts = line.strip().split(",")
+            if len(parts) == 3 and parts[0] in ("dram__bytes_read.sum", "dram__bytes_write.sum"):
+                tot += float(parts[2]) * {"Mbyte": 1e6, "Gbyte": 1e9, "Kbyte": 1e3, "byte": 1.0}[parts[1]]
+        return tot or None
+    except Exception:
+        return None
+
+
 def kernel_roofline(model, prec_name, n_rays, reps):
     """The dominant kernel alone: fused MLP forward over the fine pass of one step (n_rays x 192 points)."""
     import nerf_kinematics_b200 as nk  # noqa: F401
@@ -308,7 +322,8 @@ def run_ours(args):
             "gpu_launches": int(launches),
             "clocks": clocks,
             "roofline": {"bound": "tensor", "kernel": "fused MLP forward (%s), %d points" % (prec_name, pts),
-                         "achieved": tf, "peak": peak, "unit": "TFLOP/s", "frac": tf / peak, "traffic": None,
+                         "achieved": tf, "peak": peak, "unit": "TFLOP/s", "frac": tf / peak,
+                         "traffic": profiled_traffic_bytes() if prec_name == "bf16" else None,
                          "peak_source": pk["source"], "ms_per_launch": 1e3 * t_kernel,
                          "step_frac_of_tensor_peak": value / world * FLOPS_PER_RAY_TRAIN / 1e12 / peak},
             "cpu_baseline": {"value": cpu_rate, "unit": "rays/s", "cores": threads, "kind": "port",
