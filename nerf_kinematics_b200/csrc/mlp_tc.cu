@@ -47,7 +47,8 @@ __device__ __forceinline__ void pack_weights_body(const float* __restrict__ para
 #pragma unroll
   for (int e = 0; e < 8; ++e) {
     const int k = c * 8 + e;
-    v[e] = k < sg.ncols ? src[k] : 0.0f;
+    // element 63 multiplies the encoding block's constant-one channel: the layer's bias rides along in the MMA
+    v[e] = k < sg.ncols ? src[k] : (k == 63 && sg.bias_off >= 0 ? params[sg.bias_off + r] : 0.0f);
   }
   uint4 pk;
   pk.x = pack_h2(v[0], v[1], false);
@@ -131,7 +132,7 @@ __device__ __forceinline__ void encode_row(unsigned char* block, int row, float 
       s[k] = s2; c[k] = c2;
     }
   }
-  ch[63] = 0.0f;
+  ch[63] = 1.0f;  // constant-one channel: element 63 of a layer's encoding weights holds its bias (pack_weights_body)
   unsigned char* rp = block + row * 128;
 #pragma unroll
   for (int q = kChunk0; q < kChunk0 + kChunks; ++q) {
@@ -157,16 +158,15 @@ __device__ __forceinline__ void sts_u4(uint32_t saddr, const uint4& v) {
 // accumulator columns [c0, c0+32) of one row (+ bias, optional ReLU) -> 16-bit -> four swizzled 16-byte chunks of the
 // row's 128-byte line at rp; kAlpha also accumulates <activation, alpha weights> in fp32
 template <bool kAlpha>
-__device__ __forceinline__ void epi_convert32(const uint32_t (&v)[64], int c0, uint32_t rp, uint32_t bj, uint32_t wa, int sw,
+__device__ __forceinline__ void epi_convert32(const uint32_t (&v)[64], int c0, uint32_t rp, uint32_t wa, int sw,
                                               bool relu, float& adot) {
 #pragma unroll
   for (int c = 0; c < 4; ++c) {
     const int e0 = c0 + 8 * c;
-    const float4 b0 = lds_f4(bj + 4 * e0), b1 = lds_f4(bj + 4 * e0 + 16);
-    const float a0 = __uint_as_float(v[e0 + 0]) + b0.x, a1 = __uint_as_float(v[e0 + 1]) + b0.y;
-    const float a2 = __uint_as_float(v[e0 + 2]) + b0.z, a3 = __uint_as_float(v[e0 + 3]) + b0.w;
-    const float a4 = __uint_as_float(v[e0 + 4]) + b1.x, a5 = __uint_as_float(v[e0 + 5]) + b1.y;
-    const float a6 = __uint_as_float(v[e0 + 6]) + b1.z, a7 = __uint_as_float(v[e0 + 7]) + b1.w;
+    const float a0 = __uint_as_float(v[e0 + 0]), a1 = __uint_as_float(v[e0 + 1]);
+    const float a2 = __uint_as_float(v[e0 + 2]), a3 = __uint_as_float(v[e0 + 3]);
+    const float a4 = __uint_as_float(v[e0 + 4]), a5 = __uint_as_float(v[e0 + 5]);
+    const float a6 = __uint_as_float(v[e0 + 6]), a7 = __uint_as_float(v[e0 + 7]);
     if (kAlpha) {
       const float4 w0 = lds_f4(wa + 4 * e0), w1 = lds_f4(wa + 4 * e0 + 16);
       const float lo = relu ? 0.0f : -3.0e38f;
@@ -186,7 +186,7 @@ __device__ __forceinline__ void epi_convert32(const uint32_t (&v)[64], int c0, u
 
 
 // flags of the MMA issuer's step program
-enum : uint32_t { PF_WAIT_ACT = 4u, PF_WAIT_ENCD = 8u, PF_FIRST = 16u, PF_LAST = 32u, PF_ACC = 64u };
+enum : uint32_t { PF_WAIT_ACT = 4u, PF_WAIT_ENCD = 8u, PF_FIRST = 16u, PF_LAST = 32u, PF_ACC = 64u, PF_BIAS = 128u };
 // constant upper halves of the shared-memory operand descriptors (see umma_desc / umma_desc_sw64)
 constexpr uint64_t kDescHiSw128 = ((uint64_t)1 << 16) | ((uint64_t)(1024 >> 4) << 32) | ((uint64_t)1 << 46) | ((uint64_t)2 << 61);
 constexpr uint64_t kDescHiSw64 = ((uint64_t)1 << 16) | ((uint64_t)(512 >> 4) << 32) | ((uint64_t)1 << 46) | ((uint64_t)4 << 61);
@@ -239,24 +239,28 @@ mlp_tc_kernel(const __grid_constant__ TcPlan plan, const unsigned char* __restri
     // step program: x = byte offset of the A operand half-block inside a tile's region, y = instruction descriptor,
     // z = flags (PF_*; bits 0-1 = activation block to wait for), w = X-record block the awaited operand is saved to
     int i = 0;
+    bool encd_pending = false;  // the encoding block is being rewritten: its next reader waits for bar_encd
     for (int s = 0; s < plan.n_stages; ++s) {
       const TcStage& st = plan.st[s];
       for (int kb = 0; kb < st.n_kb; ++kb) {
         const int sidx = st.a_src[kb];
-        for (int h = 0; h < 2; ++h) {
+        // SRC_BIAS: one K=16 MMA over channels 48..63 of the encoding block (channel 63 == 1) against a chunk that is
+        // zero except for the biases in element 63 -- only the second half-block of that chunk is ever loaded
+        for (int h = sidx == SRC_BIAS ? 1 : 0; h < 2; ++h) {
           uint4 e;
           e.x = (uint32_t)((sidx < 4 ? sidx : plan.n_act_blocks) * kBlockBytes + h * 64);
           e.y = umma_idesc(st.n_main);
-          e.z = 0u;
+          e.z = sidx == SRC_BIAS ? PF_BIAS : 0u;
           e.w = 0u;
           if (h == 0 && sidx < 4) { e.z |= PF_WAIT_ACT | (uint32_t)sidx; e.w = (uint32_t)(plan.st[s - 1].rec_blk + sidx); }
-          if (h == 0 && sidx == SRC_ENCD) { e.z |= PF_WAIT_ENCD; e.w = 1u; }
+          if ((sidx == SRC_ENCD || sidx == SRC_BIAS) && encd_pending) { e.z |= PF_WAIT_ENCD; e.w = 1u; encd_pending = false; }
           if (kb == 0 && h == 0) e.z |= PF_FIRST;
           if (kb == st.n_kb - 1 && h == 1) e.z |= PF_LAST;
           if ((kb | h) != 0) e.z |= PF_ACC;
           prog[i++] = e;
         }
       }
+      if (st.write_encd) encd_pending = true;
     }
   }
   if (warp == 1) {  // TMEM: all 512 columns (one CTA per SM): tile t owns columns [256 t, 256 t + 256)
@@ -277,7 +281,7 @@ mlp_tc_kernel(const __grid_constant__ TcPlan plan, const unsigned char* __restri
         for (int s = 0; s < plan.n_stages; ++s) {
           const TcStage& st = plan.st[s];
           for (int kb = 0; kb < st.n_kb; ++kb) {
-            for (int h = 0; h < 2; ++h) {
+            for (int h = st.a_src[kb] == SRC_BIAS ? 1 : 0; h < 2; ++h) {
               const uint32_t bytes = (uint32_t)st.n_main * 64u;
               mbar_wait(smem_u32(bar_empty + slot), phase ^ 1);
               const uint32_t fb = smem_u32(bar_full + slot);
@@ -360,7 +364,7 @@ mlp_tc_kernel(const __grid_constant__ TcPlan plan, const unsigned char* __restri
         const uint64_t a_desc = kDescHiSw128 | (uint64_t)(((act_s + e.x) & 0x3FFFFu) >> 4);
         const uint64_t b_desc = kDescHiSw64 | (uint64_t)(((ring_s + slot * kFwdSlotBytes) & 0x3FFFFu) >> 4);
         if (elect_one()) {
-          tc_mma(d_tmem, a_desc, b_desc, e.y, (fl & PF_ACC) ? 1u : 0u);
+          if (!(fl & PF_BIAS)) tc_mma(d_tmem, a_desc, b_desc, e.y, (fl & PF_ACC) ? 1u : 0u);
           tc_mma(d_tmem, a_desc + 2, b_desc + 2, e.y, 1u);
           tc_commit(bar_empty_s + 8 * slot);  // (1 of 2 arrivals) frees the ring slot when these MMAs have read it
           if (fl & PF_LAST) {
@@ -448,14 +452,13 @@ mlp_tc_kernel(const __grid_constant__ TcPlan plan, const unsigned char* __restri
             }
             if (dbg & 2) { fence_async_smem(); mbar_arrive(smem_u32(bar_act + 4 * t + j)); continue; }
             const uint32_t rp = smem_u32(act_t) + j * kBlockBytes + row * 128;
-            const uint32_t bj = smem_u32(bs) + j * 256;
             if (st.alpha_dot) {
               const uint32_t wa = smem_u32(bias_s) + (plan.alpha_w_off + j * 64) * 4;
-              epi_convert32<true>(v, 0, rp, bj, wa, sw, relu, adot);
-              epi_convert32<true>(v, 32, rp, bj, wa, sw, relu, adot);
+              epi_convert32<true>(v, 0, rp, wa, sw, relu, adot);
+              epi_convert32<true>(v, 32, rp, wa, sw, relu, adot);
             } else {
-              epi_convert32<false>(v, 0, rp, bj, 0u, sw, relu, adot);
-              epi_convert32<false>(v, 32, rp, bj, 0u, sw, relu, adot);
+              epi_convert32<false>(v, 0, rp, 0u, sw, relu, adot);
+              epi_convert32<false>(v, 32, rp, 0u, sw, relu, adot);
             }
             fence_async_smem();
             mbar_arrive(smem_u32(bar_act + 4 * t + j));
@@ -520,7 +523,7 @@ static bool build_plan(const Graph& g, TcPlan& plan, std::vector<PackSeg>& segs,
   *why = nullptr;
   if (g.width % 128 != 0 || g.width > 256) { *why = "width must be 128 or 256"; return false; }
   if (g.use_viewdirs && (g.feat_width % 64 != 0 || g.feat_width > 256)) { *why = "feature width must be <= 256"; return false; }
-  if (g.Cx > 64 || g.Cd > 64) { *why = "more than 10 encoding frequencies"; return false; }
+  if (g.Cx > 63 || g.Cd > 63) { *why = "more than 10 encoding frequencies"; return false; }
   if (g.skip >= g.depth - 1) { *why = "skip connection after the last trunk layer"; return false; }
   const int wb = g.width / 64;
   plan.n_act_blocks = std::max(wb, g.use_viewdirs ? g.feat_width / 64 : 0);
@@ -548,8 +551,12 @@ static bool build_plan(const Graph& g, TcPlan& plan, std::vector<PackSeg>& segs,
     st.a_src[st.n_kb++] = a_src;
     woff += st.chunk_bytes;
   };
+  // hidden layers get their bias through the MMA: as element 63 of the encoding weights where the layer reads an
+  // encoding block anyway, else as one extra K=16 step (SRC_BIAS) at the end of the stage
+  auto with_bias = [](PackSeg sg, const Lin& l) { sg.bias_off = l.b_off; return sg; };
   auto seg = [](const Lin& l, int row0, int col0, int ncols) {
     PackSeg s{};
+    s.bias_off = -1;
     s.src_off = l.w_off; s.row0 = row0; s.n_rows = l.out; s.ld = l.in; s.col0 = col0; s.ncols = ncols;
     return s;
   };
@@ -560,15 +567,16 @@ static bool build_plan(const Graph& g, TcPlan& plan, std::vector<PackSeg>& segs,
     TcStage& st = begin_stage(g.width, EPI_HIDDEN, !(i == 0 && !g.act0), g.width);
     bsegs.push_back(BiasSeg{st.b_off, l.out, l.b_off});
     if (i == 0) {
-      add_kb(st, SRC_ENCX, seg(l, 0, 0, g.Cx));
+      add_kb(st, SRC_ENCX, with_bias(seg(l, 0, 0, g.Cx), l));
     } else {
       int off = 0;
       if (i - 1 == g.skip) {
-        add_kb(st, SRC_ENCX, seg(l, 0, 0, g.Cx));
+        add_kb(st, SRC_ENCX, with_bias(seg(l, 0, 0, g.Cx), l));
         off = g.Cx;
         last_encx = i;
       }
       for (int j = 0; j < wb; ++j) add_kb(st, j, seg(l, 0, off + 64 * j, 64));
+      if (off == 0) add_kb(st, SRC_BIAS, with_bias(seg(l, 0, 0, 0), l));
     }
   }
   if (g.use_viewdirs) {
@@ -590,10 +598,12 @@ static bool build_plan(const Graph& g, TcPlan& plan, std::vector<PackSeg>& segs,
     TcStage& sh = begin_stage(g.feat_width, EPI_HIDDEN, g.feat_act ? 1 : 0, g.feat_width);
     bsegs.push_back(BiasSeg{sh.b_off, lf.out, lf.b_off});
     for (int j = 0; j < wb; ++j) add_kb(sh, j, seg(lf, 0, 64 * j, 64));
+    add_kb(sh, SRC_BIAS, with_bias(seg(lf, 0, 0, 0), lf));
     TcStage& sd = begin_stage(g.dir_width, EPI_HIDDEN, 1, g.dir_width);
     bsegs.push_back(BiasSeg{sd.b_off, ld.out, ld.b_off});
     for (int j = 0; j < g.feat_width / 64; ++j) add_kb(sd, j, seg(ld, 0, 64 * j, 64));
-    if (g.Cd > 0) add_kb(sd, SRC_ENCD, seg(ld, 0, g.feat_width, g.Cd));
+    if (g.Cd > 0) add_kb(sd, SRC_ENCD, with_bias(seg(ld, 0, g.feat_width, g.Cd), ld));
+    else add_kb(sd, SRC_BIAS, with_bias(seg(ld, 0, 0, 0), ld));
     TcStage& sr = begin_stage(16, EPI_RGB, 0, 0);
     bsegs.push_back(BiasSeg{sr.b_off, 3, lr.b_off});
     for (int j = 0; j < g.dir_width / 64; ++j) add_kb(sr, j, seg(lr, 0, 64 * j, 64));
@@ -607,7 +617,8 @@ static bool build_plan(const Graph& g, TcPlan& plan, std::vector<PackSeg>& segs,
     if (plan.st[s].n_kb > kMaxKB) { *why = "too many K blocks"; return false; }
   plan.n_bias = boff;
   plan.n_steps = 0;
-  for (int s = 0; s < plan.n_stages; ++s) plan.n_steps += 2 * plan.st[s].n_kb;
+  for (int s = 0; s < plan.n_stages; ++s)
+    for (int kb = 0; kb < plan.st[s].n_kb; ++kb) plan.n_steps += plan.st[s].a_src[kb] == SRC_BIAS ? 1 : 2;
   w_bytes = woff;
   return true;
 }

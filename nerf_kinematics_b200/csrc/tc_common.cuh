@@ -14,7 +14,7 @@ constexpr int kMaxKB = 6;
 constexpr int kRing = 3;
 constexpr int kTileM = 128;
 constexpr int kBlockBytes = kTileM * 128;  // one 128-row x 64-element 16-bit K-block, SWIZZLE_128B
-enum { SRC_ENCX = 4, SRC_ENCD = 5, SRC_DRAW = 6 };
+enum { SRC_ENCX = 4, SRC_ENCD = 5, SRC_DRAW = 6, SRC_BIAS = 7 };
 enum { EPI_HIDDEN = 0, EPI_RGB = 2, EPI_OUT4 = 3 };
 // forward kernel: weight producer warp, 2 MMA issuer warps (one per tile), a spare warp, 2 tiles x 8 epilogue warps
 constexpr int kThreadsTc = 640;
@@ -94,6 +94,7 @@ struct WgPlan {
 struct PackSeg {
   long long dst_off;  // bytes, start of the chunk in the packed image
   long long src_off;  // floats, start of the source matrix in the flat parameters
+  long long bias_off; // floats, the layer's bias vector (written to chunk element 63), -1 = none
   int row0, n_rows;   // chunk rows [row0, row0+n_rows) <- source rows [0, n_rows)
   int chunk_rows;     // rows of the whole chunk (the stage's N)
   int ld, col0, ncols;  // source leading dim; chunk element k <- source column col0+k for k < ncols, else 0
