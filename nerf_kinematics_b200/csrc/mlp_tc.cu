@@ -157,9 +157,10 @@ __device__ __forceinline__ void sts_u4(uint32_t saddr, const uint4& v) {
 }
 // accumulator columns [c0, c0+32) of one row (+ bias, optional ReLU) -> 16-bit -> four swizzled 16-byte chunks of the
 // row's 128-byte line at rp; kAlpha also accumulates <activation, alpha weights> in fp32
-template <bool kAlpha>
+template <bool kAlpha, int kRelu = -1>  // kRelu: 0 / 1 = compile-time activation choice, -1 = the run-time flag
 __device__ __forceinline__ void epi_convert32(const uint32_t (&v)[64], int c0, uint32_t rp, uint32_t wa, int sw,
-                                              bool relu, float& adot) {
+                                              bool relu_rt, float& adot) {
+  const bool relu = kRelu < 0 ? relu_rt : kRelu != 0;
 #pragma unroll
   for (int c = 0; c < 4; ++c) {
     const int e0 = c0 + 8 * c;
@@ -456,9 +457,12 @@ mlp_tc_kernel(const __grid_constant__ TcPlan plan, const unsigned char* __restri
               const uint32_t wa = smem_u32(bias_s) + (plan.alpha_w_off + j * 64) * 4;
               epi_convert32<true>(v, 0, rp, wa, sw, relu, adot);
               epi_convert32<true>(v, 32, rp, wa, sw, relu, adot);
+            } else if (relu) {  // the common case without a branch per 16-byte chunk
+              epi_convert32<false, 1>(v, 0, rp, 0u, sw, true, adot);
+              epi_convert32<false, 1>(v, 32, rp, 0u, sw, true, adot);
             } else {
-              epi_convert32<false>(v, 0, rp, 0u, sw, relu, adot);
-              epi_convert32<false>(v, 32, rp, 0u, sw, relu, adot);
+              epi_convert32<false, 0>(v, 0, rp, 0u, sw, false, adot);
+              epi_convert32<false, 0>(v, 32, rp, 0u, sw, false, adot);
             }
             fence_async_smem();
             mbar_arrive(smem_u32(bar_act + 4 * t + j));
