@@ -142,7 +142,7 @@ def profiled_traffic_bytes():
     workload) from the committed `ncu --set full` capture under profiles/; None if the summary is missing."""
     try:
         tot = 0.0
-        for line in open(os.path.join(ROOT, "profiles", "r1b_mlp_tc_pair_kernel_ncu_full.csv")):
+        for line in open(os.path.join(ROOT, "profiles", "r1c_mlp_tc_pair_kernel_ncu_full.csv")):
             parts = line.strip().split(",")
             if len(parts) == 3 and parts[0] in ("dram__bytes_read.sum", "dram__bytes_write.sum"):
                 tot += float(parts[2]) * {"Mbyte": 1e6, "Gbyte": 1e9, "Kbyte": 1e3, "byte": 1.0}[parts[1]]
