@@ -225,7 +225,7 @@ def run_ours(args):
         prec_name = "bf16" if getattr(nk, "BF16_BACKWARD", False) else "fp32"
     step = TrainStep(mc, mf, N_samples=N_SAMPLES, N_importance=N_IMPORTANCE, perturb=1.0, raw_noise_std=0.0,
                      white_bkgd=True, precision=prec_name, lrate=5e-4, lrate_decay=500, world_size=world,
-                     cuda_graph=not args.no_graph)
+                     cuda_graph=not args.no_graph, seed=1234 + rank)  # jitter + inverse-CDF uniforms drawn in-kernel (f4)
     # ---- synthetic inputs of the named shape: one 800x800 pose, N_rand rays per step without replacement
     c2w = torch.from_numpy(pose_spherical(30.0 + 7.0 * rank, -30.0, 4.0))
     ro, rd = nk.get_rays(H, W, FOCAL, c2w)

@@ -212,7 +212,23 @@ typedef struct nb_render_rand {
   const float* u_fine;  /* [n, n_importance] uniforms for sample_pdf (run_nerf_helpers.py:192-197) */
   const float* noise_c; /* [n, n_samples] sigma noise, already scaled by raw_noise_std (run_nerf.py:130-132) */
   const float* noise_f; /* [n, n_samples + n_importance] */
+  /* in-kernel generator.  With philox_state != NULL (device, {seed, step}), every input above that is
+   * NULL but asked for -- the jitter and the inverse-CDF uniforms when perturb != 0, the sigma noise when
+   * raw_noise_std > 0 -- is drawn inside the sampling / compositing kernels (Philox4x32-10, counter = ray, sample,
+   * input, step), statistically (not bitwise) matched to the reference's framework generator.  The backward call must
+   * see the same state as its forward; nb_rng_advance moves to the next step. */
+  const uint64_t* philox_state;
+  int perturb;
+  float raw_noise_std;
 } nb_render_rand;
+
+/* f4: state[1] += 1 on the stream (graph-capturable: a captured train step draws fresh numbers on every replay). */
+int nb_rng_advance(uint64_t* state, nb_stream_t stream);
+/* f4: the numbers the kernels draw, as an array: out[r, s] for r < n, s < row_len; input = 0 jitter, 1 inverse-CDF
+ * uniforms, 2 coarse noise, 3 fine noise; normal != 0 -> scale * N(0,1), else U[0,1).  Feeding these arrays back
+ * through t_rand / u_fine / noise_* reproduces the in-kernel result bit for bit (tests/test_gpu_rng.py). */
+int nb_rng_fill(const uint64_t* state, int input, int normal, float scale, int64_t n, int row_len, float* out,
+                nb_stream_t stream);
 
 /* Outputs (device, any may be NULL).  With n_importance == 0 the coarse result is written to
  * rgb/disp/acc/depth and the *0 pointers are ignored. */

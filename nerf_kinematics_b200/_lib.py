@@ -27,7 +27,8 @@ class RenderCfg(C.Structure):  # nb_render_cfg
 
 
 class RenderRand(C.Structure):  # nb_render_rand
-    _fields_ = [("t_rand", p), ("u_fine", p), ("noise_c", p), ("noise_f", p)]
+    _fields_ = [("t_rand", p), ("u_fine", p), ("noise_c", p), ("noise_f", p), ("philox_state", p), ("perturb", C.c_int),
+                ("raw_noise_std", C.c_float)]
 
 
 class RenderOut(C.Structure):  # nb_render_out
@@ -57,6 +58,8 @@ SIGNATURES = {
     "nb_get_rays": (i32, [i32, i32, f32, f32, f32, f32, C.POINTER(f32), i32, i32, p, p, p]),
     "nb_get_rays_at": (i32, [i32, i32, f32, f32, f32, f32, C.POINTER(f32), p, i64, p, p, p]),
     "nb_to8b": (i32, [p, p, i64, p, p, p]),
+    "nb_rng_advance": (i32, [p, p]),
+    "nb_rng_fill": (i32, [p, i32, i32, f32, i64, i32, p, p]),
     "nb_ndc_rays": (i32, [i32, i32, f64, f64, p, p, i64, p, p, p]),
     "nb_make_ray_batch": (i32, [p, p, p, i64, i32, i32, i32, i32, f64, f64, f64, p, p, p, p]),
     "nb_sample_coarse": (i32, [p, i32, i64, i32, i32, p, p, p]),

@@ -47,6 +47,20 @@ static RenderLayout render_layout(const nb_model* coarse, const nb_model* fine, 
 
 static inline float* at(void* ws, size_t off) { return reinterpret_cast<float*>(static_cast<char*>(ws) + off); }
 
+// which of the four random inputs come from the in-kernel generator (f4): those the caller asked for (perturb /
+// raw_noise_std) without supplying an array
+struct RenderRng {
+  Rng jitter, fine_u, noise_c, noise_f;
+  explicit RenderRng(const nb_render_rand& r) {
+    const unsigned long long* st = reinterpret_cast<const unsigned long long*>(r.philox_state);
+    const bool jit = st != nullptr && r.perturb != 0, noi = st != nullptr && r.raw_noise_std > 0.0f;
+    jitter = Rng{jit && r.t_rand == nullptr ? st : nullptr, RNG_JITTER, 0.0f};
+    fine_u = Rng{jit && r.u_fine == nullptr ? st : nullptr, RNG_FINE_U, 0.0f};
+    noise_c = Rng{noi && r.noise_c == nullptr ? st : nullptr, RNG_NOISE_C, r.raw_noise_std};
+    noise_f = Rng{noi && r.noise_f == nullptr ? st : nullptr, RNG_NOISE_F, r.raw_noise_std};
+  }
+};
+
 }  // namespace nb
 
 using namespace nb;
@@ -85,8 +99,9 @@ int nb_render_rays(const nb_model_t* coarse, const nb_model_t* fine, const float
     set_error("nb_render_rays: workspace of %zu bytes given, %zu needed", ws_bytes, L.total);
     return NB_ERR_WORKSPACE;
   }
-  const nb_render_rand none{nullptr, nullptr, nullptr, nullptr};
+  const nb_render_rand none{nullptr, nullptr, nullptr, nullptr, nullptr, 0, 0.0f};
   const nb_render_rand& r = rnd ? *rnd : none;
+  const RenderRng rr(r);
   const int S = cfg->n_samples, I = cfg->n_importance;
   const bool hier = I > 0;
   float* zc = at(ws, L.off_zc);
@@ -96,13 +111,13 @@ int nb_render_rays(const nb_model_t* coarse, const nb_model_t* fine, const float
   void* mlp_c = static_cast<char*>(ws) + L.off_mlp_c;
   void* mlp_f = static_cast<char*>(ws) + L.off_mlp_f;
 
-  NB_TRY(nb_sample_coarse(rays, ray_stride, n, S, cfg->lindisp, r.t_rand, zc, stream));
+  NB_TRY(sample_coarse_impl(rays, ray_stride, n, S, cfg->lindisp, r.t_rand, rr.jitter, zc, stream));
   NB_TRY(nb_mlp_forward(coarse, cfg->precision, rays, ray_stride, zc, n, S, rawc, mlp_c, L.mlp_c_bytes,
                         cfg->save_for_backward, stream));
   // coarse compositing; its weights feed sample_pdf
   float* c_rgb = hier ? (out->rgb0 ? out->rgb0 : scratch) : (out->rgb ? out->rgb : scratch);
-  NB_TRY(nb_composite(rawc, zc, rays, ray_stride, n, S, r.noise_c, cfg->white_bkgd, c_rgb, hier ? out->disp0 : out->disp,
-                      hier ? out->acc0 : out->acc, hier ? out->depth0 : out->depth, wc, stream));
+  NB_TRY(composite_impl(rawc, zc, rays, ray_stride, n, S, r.noise_c, rr.noise_c, cfg->white_bkgd, c_rgb,
+                        hier ? out->disp0 : out->disp, hier ? out->acc0 : out->acc, hier ? out->depth0 : out->depth, wc, stream));
   const float* last_raw = rawc;
   const float* last_z = zc;
   const float* last_w = wc;
@@ -110,12 +125,12 @@ int nb_render_rays(const nb_model_t* coarse, const nb_model_t* fine, const float
   if (hier) {
     float* zf = at(ws, L.off_zf);
     float* rawf = at(ws, L.off_rawf);
-    NB_TRY(nb_sample_fine(zc, wc, n, S, r.u_fine, I, nullptr, zf, out->z_std, stream));
+    NB_TRY(sample_fine_impl(zc, wc, n, S, r.u_fine, rr.fine_u, I, nullptr, zf, out->z_std, stream));
     const nb_model_t* mf = fine ? fine : coarse;
     NB_TRY(nb_mlp_forward(mf, cfg->precision, rays, ray_stride, zf, n, S + I, rawf, mlp_f, L.mlp_f_bytes,
                           cfg->save_for_backward, stream));
-    NB_TRY(nb_composite(rawf, zf, rays, ray_stride, n, S + I, r.noise_f, cfg->white_bkgd, out->rgb ? out->rgb : scratch,
-                        out->disp, out->acc, out->depth, out->weights, stream));
+    NB_TRY(composite_impl(rawf, zf, rays, ray_stride, n, S + I, r.noise_f, rr.noise_f, cfg->white_bkgd,
+                          out->rgb ? out->rgb : scratch, out->disp, out->acc, out->depth, out->weights, stream));
     last_raw = rawf;
     last_z = zf;
     last_w = nullptr;  // written directly above
@@ -142,8 +157,9 @@ int nb_render_rays_backward(const nb_model_t* coarse, const nb_model_t* fine, co
     set_error("nb_render_rays_backward: workspace of %zu bytes given, %zu needed", ws_bytes, L.total);
     return NB_ERR_WORKSPACE;
   }
-  const nb_render_rand none{nullptr, nullptr, nullptr, nullptr};
+  const nb_render_rand none{nullptr, nullptr, nullptr, nullptr, nullptr, 0, 0.0f};
   const nb_render_rand& r = rnd ? *rnd : none;
+  const RenderRng rr(r);
   const int S = cfg->n_samples, I = cfg->n_importance;
   const bool hier = I > 0;
   float* draw = at(ws, L.off_draw);
@@ -154,18 +170,18 @@ int nb_render_rays_backward(const nb_model_t* coarse, const nb_model_t* fine, co
     float* gf = fine ? grad_fine : grad_coarse;
     NB_REQUIRE(gf != nullptr, "nb_render_rays_backward: null grad_fine");
     if (g->d_rgb || g->d_disp || g->d_acc || g->d_depth) {
-      NB_TRY(nb_composite_backward(at(ws, L.off_rawf), at(ws, L.off_zf), rays, ray_stride, n, S + I, r.noise_f,
-                                   cfg->white_bkgd, g->d_rgb, g->d_disp, g->d_acc, g->d_depth, draw, stream));
+      NB_TRY(composite_backward_impl(at(ws, L.off_rawf), at(ws, L.off_zf), rays, ray_stride, n, S + I, r.noise_f,
+                                     rr.noise_f, cfg->white_bkgd, g->d_rgb, g->d_disp, g->d_acc, g->d_depth, draw, stream));
       NB_TRY(nb_mlp_backward(mf, cfg->precision, n * (S + I), draw, mlp_f, L.mlp_f_bytes, gf, stream));
     }
     if (g->d_rgb0 || g->d_disp0 || g->d_acc0 || g->d_depth0) {
-      NB_TRY(nb_composite_backward(at(ws, L.off_rawc), at(ws, L.off_zc), rays, ray_stride, n, S, r.noise_c,
-                                   cfg->white_bkgd, g->d_rgb0, g->d_disp0, g->d_acc0, g->d_depth0, draw, stream));
+      NB_TRY(composite_backward_impl(at(ws, L.off_rawc), at(ws, L.off_zc), rays, ray_stride, n, S, r.noise_c,
+                                   rr.noise_c, cfg->white_bkgd, g->d_rgb0, g->d_disp0, g->d_acc0, g->d_depth0, draw, stream));
       NB_TRY(nb_mlp_backward(coarse, cfg->precision, n * S, draw, mlp_c, L.mlp_c_bytes, grad_coarse, stream));
     }
   } else if (g->d_rgb || g->d_disp || g->d_acc || g->d_depth) {
-    NB_TRY(nb_composite_backward(at(ws, L.off_rawc), at(ws, L.off_zc), rays, ray_stride, n, S, r.noise_c,
-                                 cfg->white_bkgd, g->d_rgb, g->d_disp, g->d_acc, g->d_depth, draw, stream));
+    NB_TRY(composite_backward_impl(at(ws, L.off_rawc), at(ws, L.off_zc), rays, ray_stride, n, S, r.noise_c,
+                                 rr.noise_c, cfg->white_bkgd, g->d_rgb, g->d_disp, g->d_acc, g->d_depth, draw, stream));
     NB_TRY(nb_mlp_backward(coarse, cfg->precision, n * S, draw, mlp_c, L.mlp_c_bytes, grad_coarse, stream));
   }
   return NB_OK;

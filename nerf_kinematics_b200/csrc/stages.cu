@@ -179,19 +179,31 @@ __device__ __forceinline__ float coarse_z(float near, float far, int s, int S, i
 }
 
 __global__ void sample_coarse_kernel(const float* __restrict__ rays, int stride, int64_t n, int S, int lindisp,
-                                     const float* __restrict__ t_rand, float* __restrict__ z) {
+                                     const float* __restrict__ t_rand, Rng rng, float* __restrict__ z) {
   int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (idx >= n * S) return;
   int64_t r = idx / S;
   int s = (int)(idx - r * S);
   float near = rays[r * stride + 6], far = rays[r * stride + 7];
   float zc = coarse_z(near, far, s, S, lindisp);
-  if (t_rand) {
+  if (t_rand != nullptr || rng.state != nullptr) {
     float lower = (s == 0) ? zc : 0.5f * (zc + coarse_z(near, far, s - 1, S, lindisp));
     float upper = (s == S - 1) ? zc : 0.5f * (coarse_z(near, far, s + 1, S, lindisp) + zc);
-    zc = lower + (upper - lower) * t_rand[idx];
+    zc = lower + (upper - lower) * (t_rand != nullptr ? t_rand[idx] : rng_uniform(rng, r, s));
   }
   z[idx] = zc;
+}
+
+// f4: the generator's step counter lives on the device so that a captured train step advances it on every replay
+__global__ void rng_advance_kernel(unsigned long long* state) { state[1] += 1ull; }
+
+// the numbers the kernels draw for rows of length row_len, as arrays (tests; hosts that want to log them)
+__global__ void rng_fill_kernel(Rng rng, int normal, int64_t n, int row_len, float* __restrict__ out) {
+  const int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= n * row_len) return;
+  const int64_t r = idx / row_len;
+  const int s = (int)(idx - r * row_len);
+  out[idx] = normal ? rng_normal(rng, r, s) : rng_uniform(rng, r, s);
 }
 
 // ------------------------------------------------------------------------------------ a6
@@ -234,6 +246,15 @@ __global__ void mse_kernel(const float* __restrict__ pred, const float* __restri
     v = warp_sum(v);
     if (lane == 0) atomicAdd(loss, v * inv);
   }
+}
+
+int sample_coarse_impl(const float* rays, int stride, int64_t n, int S, int lindisp, const float* t_rand, Rng rng, float* z,
+                       nb_stream_t stream) {
+  NB_REQUIRE(n >= 0 && S > 0 && (stride == 8 || stride == 11) && (n == 0 || (rays && z)), "nb_sample_coarse: bad arguments");
+  if (n == 0) return NB_OK;
+  sample_coarse_kernel<<<(unsigned)ceil_div(n * S, 256), 256, 0, as_stream(stream)>>>(rays, stride, n, S, lindisp, t_rand, rng, z);
+  NB_LAUNCHED();
+  return NB_OK;
 }
 
 }  // namespace nb
@@ -334,9 +355,24 @@ int nb_make_ray_batch(const float* ro, const float* rd, const float* vsrc, int64
 
 int nb_sample_coarse(const float* rays, int stride, int64_t n, int S, int lindisp, const float* t_rand, float* z,
                      nb_stream_t stream) {
-  NB_REQUIRE(n >= 0 && S > 0 && (stride == 8 || stride == 11) && (n == 0 || (rays && z)), "nb_sample_coarse: bad arguments");
+  return nb::sample_coarse_impl(rays, stride, n, S, lindisp, t_rand, Rng{nullptr, 0u, 0.0f}, z, stream);
+}
+
+int nb_rng_advance(uint64_t* state, nb_stream_t stream) {
+  NB_REQUIRE(state != nullptr, "nb_rng_advance: null state");
+  rng_advance_kernel<<<1, 1, 0, as_stream(stream)>>>(reinterpret_cast<unsigned long long*>(state));
+  NB_LAUNCHED();
+  return NB_OK;
+}
+
+int nb_rng_fill(const uint64_t* state, int stream_id, int normal, float scale, int64_t n, int row_len, float* out,
+                nb_stream_t stream) {
+  NB_REQUIRE(state != nullptr && stream_id >= 0 && stream_id < 4 && n >= 0 && row_len > 0 && row_len <= 65536 &&
+                 (n == 0 || out != nullptr),
+             "nb_rng_fill: bad arguments");
   if (n == 0) return NB_OK;
-  sample_coarse_kernel<<<(unsigned)ceil_div(n * S, 256), 256, 0, as_stream(stream)>>>(rays, stride, n, S, lindisp, t_rand, z);
+  const Rng rng{reinterpret_cast<const unsigned long long*>(state), (unsigned)stream_id, scale};
+  rng_fill_kernel<<<(unsigned)ceil_div(n * row_len, 256), 256, 0, as_stream(stream)>>>(rng, normal, n, row_len, out);
   NB_LAUNCHED();
   return NB_OK;
 }

@@ -36,7 +36,7 @@ class TrainStep:
     def __init__(self, model_coarse, model_fine, *, N_samples=64, N_importance=128, perturb=1.0, raw_noise_std=0.0,
                  white_bkgd=False, lindisp=False, precision=None, lrate=5e-4, lrate_decay=250, decay_rate=0.1,
                  eps=1e-8, betas=(0.9, 0.999), process_group=None, world_size=1, optimizer=None, fused_adam=None,
-                 tf_adam=False, cuda_graph=False):
+                 tf_adam=False, cuda_graph=False, device_rng=True, seed=0):
         self.mc, self.mf = model_coarse, (model_fine if N_importance > 0 else None)
         self.S, self.I = int(N_samples), int(N_importance)
         self.perturb, self.noise, self.white, self.lindisp = perturb, raw_noise_std, white_bkgd, lindisp
@@ -68,6 +68,11 @@ class TrainStep:
         self.opt = optimizer if optimizer is not None else torch.optim.Adam(params, lr=lrate, betas=self.betas, eps=eps)
         self.global_step = 0
         self.loss_buf = torch.zeros((2,), dtype=torch.float32, device=dev)
+        # jitter / inverse-CDF uniforms / sigma noise are drawn inside the kernels (Philox, counter =
+        # ray, sample, input, step) unless the caller injects arrays; {seed, step} lives on the device so that a
+        # captured step draws fresh numbers on every replay.  Ranks get different seeds (different rays anyway).
+        self.device_rng = bool(device_rng)
+        self.rng_state = torch.tensor([int(seed), 0], dtype=torch.int64, device=dev)
         self._ws = None
         self._ws_cache = {}
         self._graphs = {}
@@ -148,9 +153,14 @@ class TrainStep:
         hf = self.mf.prepare(self.prec, force=force_pack)[0] if self.mf is not None else None
         cfg = RenderCfg(self.S, self.I, int(self.lindisp), int(self.white), self.prec, 1)
         ws = self._workspace(n, stride, cfg, hc, hf, dev)
-        rnd = _random_inputs(n, self.S, self.I, dev, self.perturb, self.noise, rnd)
-        rs = RenderRand(_optptr(rnd.get("t_rand")), _optptr(rnd.get("u_fine")), _optptr(rnd.get("noise_c")),
-                        _optptr(rnd.get("noise_f")))
+        in_kernel = self.device_rng and rnd is None and (bool(self.perturb) or (self.noise or 0.0) > 0.0)
+        if in_kernel:
+            rs = RenderRand(None, None, None, None, C.c_void_p(self.rng_state.data_ptr()), int(bool(self.perturb)),
+                            float(self.noise or 0.0))
+        else:
+            rnd = _random_inputs(n, self.S, self.I, dev, self.perturb, self.noise, rnd)
+            rs = RenderRand(_optptr(rnd.get("t_rand")), _optptr(rnd.get("u_fine")), _optptr(rnd.get("noise_c")),
+                            _optptr(rnd.get("noise_f")))
         hier = self.I > 0
         out = {"rgb": self._out["rgb"]}
         if hier:
@@ -178,6 +188,8 @@ class TrainStep:
                                                 C.byref(rs), C.byref(gs), C.c_void_p(ws.data_ptr()), ws.numel(),
                                                 C.c_void_p(self.gc.data_ptr()), _optptr(self.gf), st),
                   "nb_render_rays_backward")
+            if in_kernel:
+                check(lib().nb_rng_advance(C.c_void_p(self.rng_state.data_ptr()), st), "nb_rng_advance")
         return self.loss_buf
 
     def allreduce(self):
