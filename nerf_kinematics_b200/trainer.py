@@ -80,6 +80,7 @@ class TrainStep:
         # NCCL collective itself (NB_SPLIT_GRAPH=0) measured the same step time on 2 B200 but left the process group
         # unable to shut down cleanly.
         self._split_graph = bool(int(os.environ.get("NB_SPLIT_GRAPH", "1")))
+        self._overlap = bool(int(os.environ.get("NB_OVERLAP_ALLREDUCE", "1")))
         self.launches_per_step = None  # kernels inside one captured iteration (graph mode)
         self.graph_replays = 0
         if self.fused:
@@ -145,8 +146,10 @@ class TrainStep:
         self._ws, self._out, self._d = ent
         return self._ws
 
-    def forward_backward(self, rays, target, rnd=None, force_pack=False, zero_bucket=True):
-        """Render + loss + backward into the flat bucket.  Returns the (device) loss tensor [2] = (fine, coarse)."""
+    def forward_backward(self, rays, target, rnd=None, force_pack=False, zero_bucket=True, phase=None):
+        """Render + loss + backward into the flat bucket.  Returns the (device) loss tensor [2] = (fine, coarse).
+        phase 1 / 2 split the call for the multi-GPU step: 1 = forward, losses and the fine network's backward,
+        2 = the coarse network's backward (so the fine gradients' all-reduce can run under it); None = everything."""
         rays, target = _f32(rays, "rays"), _f32(target, "target")
         n, stride, dev = rays.shape[0], rays.shape[1], rays.device
         hc, _ = self.mc.prepare(self.prec, force=force_pack)
@@ -169,26 +172,31 @@ class TrainStep:
         scale = 1.0 / self.world  # the mean over the global batch: each rank contributes its share
         with torch.cuda.device(dev):
             st = _stream()
-            check(lib().nb_render_rays(hc, hf, C.c_void_p(rays.data_ptr()), stride, n, C.byref(cfg), C.byref(rs),
-                                       C.byref(o), C.c_void_p(ws.data_ptr()), ws.numel(), st), "nb_render_rays")
-            self.loss_buf.zero_()
-            if zero_bucket:
-                self.bucket.zero_()
-            check(lib().nb_mse_loss(C.c_void_p(out["rgb"].data_ptr()), C.c_void_p(target.data_ptr()), n * 3, scale,
-                                    C.c_void_p(self.loss_buf.data_ptr()), C.c_void_p(self._d["rgb"].data_ptr()), st))
-            gk = {"d_rgb": self._d["rgb"]}
-            if hier:
-                check(lib().nb_mse_loss(C.c_void_p(out["rgb0"].data_ptr()), C.c_void_p(target.data_ptr()), n * 3, scale,
-                                        C.c_void_p(self.loss_buf.data_ptr() + 4), C.c_void_p(self._d["rgb0"].data_ptr()),
-                                        st))
+            if phase != 2:
+                check(lib().nb_render_rays(hc, hf, C.c_void_p(rays.data_ptr()), stride, n, C.byref(cfg), C.byref(rs),
+                                           C.byref(o), C.c_void_p(ws.data_ptr()), ws.numel(), st), "nb_render_rays")
+                self.loss_buf.zero_()
+                if zero_bucket:
+                    self.bucket.zero_()
+                check(lib().nb_mse_loss(C.c_void_p(out["rgb"].data_ptr()), C.c_void_p(target.data_ptr()), n * 3, scale,
+                                        C.c_void_p(self.loss_buf.data_ptr()), C.c_void_p(self._d["rgb"].data_ptr()), st))
+                if hier:
+                    check(lib().nb_mse_loss(C.c_void_p(out["rgb0"].data_ptr()), C.c_void_p(target.data_ptr()), n * 3,
+                                            scale, C.c_void_p(self.loss_buf.data_ptr() + 4),
+                                            C.c_void_p(self._d["rgb0"].data_ptr()), st))
+            gk = {}
+            if phase != 2:
+                gk["d_rgb"] = self._d["rgb"]
+            if hier and phase != 1:
                 gk["d_rgb0"] = self._d["rgb0"]
-            gs = RenderGrads(*[_optptr(gk.get(k)) for k in ("d_rgb", "d_disp", "d_acc", "d_depth", "d_rgb0", "d_disp0",
-                                                            "d_acc0", "d_depth0")])
-            check(lib().nb_render_rays_backward(hc, hf, C.c_void_p(rays.data_ptr()), stride, n, C.byref(cfg),
-                                                C.byref(rs), C.byref(gs), C.c_void_p(ws.data_ptr()), ws.numel(),
-                                                C.c_void_p(self.gc.data_ptr()), _optptr(self.gf), st),
-                  "nb_render_rays_backward")
-            if in_kernel:
+            if gk:
+                gs = RenderGrads(*[_optptr(gk.get(k)) for k in ("d_rgb", "d_disp", "d_acc", "d_depth", "d_rgb0",
+                                                                "d_disp0", "d_acc0", "d_depth0")])
+                check(lib().nb_render_rays_backward(hc, hf, C.c_void_p(rays.data_ptr()), stride, n, C.byref(cfg),
+                                                    C.byref(rs), C.byref(gs), C.c_void_p(ws.data_ptr()), ws.numel(),
+                                                    C.c_void_p(self.gc.data_ptr()), _optptr(self.gf), st),
+                      "nb_render_rays_backward")
+            if in_kernel and phase != 1:
                 check(lib().nb_rng_advance(C.c_void_p(self.rng_state.data_ptr()), st), "nb_rng_advance")
         return self.loss_buf
 
@@ -250,7 +258,7 @@ class TrainStep:
                 graph = torch.cuda.CUDAGraph()
                 with torch.cuda.graph(graph):
                     self._device_iteration(s_rays, s_tgt)
-                g = (graph, None, s_rays, s_tgt)
+                g = (graph, None, s_rays, s_tgt, None)
             except Exception:  # collective not capturable on this stack: capture the two local halves instead
                 if self.world == 1:
                     raise
@@ -259,12 +267,20 @@ class TrainStep:
                 self.bucket.zero_()
                 before = ops.launch_count()
         if g is None:
+            # forward + fine backward | coarse backward | Adam: the fine gradients' all-reduce runs under the coarse
+            # backward on NCCL's stream, only the coarse gradients' all-reduce is exposed
             ga, gb = torch.cuda.CUDAGraph(), torch.cuda.CUDAGraph()
+            # (host-drawn random arrays cannot be shared between two calls: that configuration keeps one backward)
+            host_rng = not self.device_rng and (bool(self.perturb) or (self.noise or 0.0) > 0.0)
+            gm = torch.cuda.CUDAGraph() if (self.mf is not None and self._overlap and not host_rng) else None
             with torch.cuda.graph(ga):
-                self.forward_backward(s_rays, s_tgt, force_pack=True, zero_bucket=False)
+                self.forward_backward(s_rays, s_tgt, force_pack=True, zero_bucket=False, phase=1 if gm is not None else None)
+            if gm is not None:
+                with torch.cuda.graph(gm):
+                    self.forward_backward(s_rays, s_tgt, force_pack=False, zero_bucket=False, phase=2)
             with torch.cuda.graph(gb):
                 self._fused_adam()
-            g = (ga, gb, s_rays, s_tgt)
+            g = (ga, gb, s_rays, s_tgt, gm)
         self.launches_per_step = ops.launch_count() - before
         self._graphs[key] = g
         return g
@@ -277,12 +293,20 @@ class TrainStep:
         self._set_hyper()
         if self.use_graph and rnd is None:
             rays, target = _f32(rays, "rays"), _f32(target, "target")
-            graph, graph_opt, s_rays, s_tgt = self._graph_for(rays, target)
+            graph, graph_opt, s_rays, s_tgt, graph_mid = self._graph_for(rays, target)
             s_rays.copy_(rays, non_blocking=True)
             s_tgt.copy_(target, non_blocking=True)
             graph.replay()
-            if graph_opt is not None:  # split mode: the all-reduce runs eagerly between the two captured halves
-                self.allreduce()
+            if graph_opt is not None:  # split mode: the all-reduces run eagerly between the captured parts
+                if graph_mid is not None:
+                    import torch.distributed as dist
+                    w_fine = dist.all_reduce(self.gf, op=dist.ReduceOp.SUM, group=self.pg, async_op=True)
+                    graph_mid.replay()
+                    w_coarse = dist.all_reduce(self.gc, op=dist.ReduceOp.SUM, group=self.pg, async_op=True)
+                    w_fine.wait()
+                    w_coarse.wait()
+                else:
+                    self.allreduce()
                 graph_opt.replay()
             self.graph_replays += 1
             loss = self.loss_buf
