@@ -28,7 +28,7 @@
 extern "C" {
 #endif
 
-#define NB_ABI_VERSION 1
+#define NB_ABI_VERSION 2 /* 2: nb_render_rand gained philox_state, perturb, raw_noise_std */
 
 typedef enum nb_status {
   NB_OK = 0,

@@ -105,8 +105,8 @@ def _load():
             fn = getattr(lib, name)  # AttributeError here == the library does not export the header
             fn.restype = res
             fn.argtypes = args
-        if lib.nb_abi_version() != 1:
-            raise NerfB200Error("libnerf_b200.so ABI version %d, binding expects 1" % lib.nb_abi_version())
+        if lib.nb_abi_version() != 2:
+            raise NerfB200Error("libnerf_b200.so ABI version %d, binding expects 2" % lib.nb_abi_version())
         _lib = lib
         return lib
 

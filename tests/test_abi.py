@@ -27,7 +27,7 @@ def test_library_exports_every_declared_symbol():
     for n in names:
         assert hasattr(lib, n), "libnerf_b200.so does not export %s" % n
     assert sorted(_lib.SIGNATURES) == names, set(names) ^ set(_lib.SIGNATURES)
-    assert _lib.lib().nb_abi_version() == 1
+    assert _lib.lib().nb_abi_version() == 2
 
 
 def test_no_torch_types_in_abi():
