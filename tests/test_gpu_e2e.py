@@ -257,3 +257,45 @@ def test_render_options_staticcam_render_factor_lindisp():
         kw2 = dict(kw, lindisp=True)
         rgb_l, _, _, ex = nk.render(H, W, f, c2w=cam_b[:3, :4], **kw2)
         assert torch.isfinite(rgb_l).all() and maxdiff(rgb_l, rgb_b) > 1e-5
+
+
+def test_full_size_lego_frame_properties_and_row_block_sharding():
+    """BASELINE configs[1] size (800 x 800, 8x256 coarse + fine, 64 + 128 samples; 640 000 rays, 123 M network points)
+    on the tensor-core path, through properties that do not need an oracle run of that size: the eight row blocks a
+    world of 8 ranks would render (parallel.render_rows, no collective) tile the single-call frame bit for bit;
+    acc = sum(weights) stays in [0, 1]; colours stay in [0, 1] under a white background; depth lies inside
+    acc * [near, far]; the chunk size does not change a value (run_nerf.py:271-272)."""
+    from nerf_kinematics_b200 import parallel
+    H = W = 800
+    focal = 1111.111
+    torch.manual_seed(11)
+    mc = nk.NeRF(D=8, W=256, input_ch=63, input_ch_views=27, skips=[4], use_viewdirs=True).to(DEV)
+    mf = nk.NeRF(D=8, W=256, input_ch=63, input_ch_views=27, skips=[4], use_viewdirs=True).to(DEV)
+    mc.precision = mf.precision = "bf16"
+    c2w = torch.tensor([[0.6, -0.5, 0.62, 2.5], [0.8, 0.37, -0.47, -1.9], [0.0, 0.78, 0.62, 2.5]])
+    kw = dict(network_query_fn=None, perturb=0.0, N_importance=128, network_fine=mf, N_samples=64, network_fn=mc,
+              white_bkgd=True, raw_noise_std=0.0, lindisp=False)
+    with torch.no_grad():
+        rgb, disp, acc, extras = nk.render(H, W, focal, chunk=1024 * 32, c2w=c2w, use_viewdirs=True, ndc=False, near=2.0,
+                                           far=6.0, **kw)
+        torch.cuda.synchronize()
+        assert rgb.shape == (H, W, 3) and bool(torch.isfinite(rgb).all()) and bool(torch.isfinite(acc).all())
+        assert float(acc.min()) >= 0.0 and float(acc.max()) <= 1.0 + 1e-5
+        assert float(rgb.min()) >= -1e-6 and float(rgb.max()) <= 1.0 + 1e-5
+        assert float(extras["acc0"].min()) >= 0.0 and float(extras["acc0"].max()) <= 1.0 + 1e-5
+        assert bool((disp[~torch.isnan(disp)] >= 0).all())
+        # the 8-rank partition: same values, no exchange
+        rows = []
+        for rank in range(8):
+            part, (r0, r1) = parallel.render_rows(H, W, focal, c2w, rank, 8, chunk=1024 * 32, near=2.0, far=6.0,
+                                                  ndc=False, use_viewdirs=True, **kw)
+            assert (r0, r1) == parallel.row_block(H, rank, 8) and part["rgb_map"].shape == (r1 - r0, W, 3)
+            rows.append(part)
+        assert torch.equal(torch.cat([p["rgb_map"] for p in rows]), rgb)
+        assert torch.equal(torch.cat([p["acc_map"] for p in rows]), acc)
+        # another chunk size on one row block
+        r0, r1 = parallel.row_block(H, 3, 8)
+        ro, rd = nk.get_rays(H, W, focal, c2w)
+        sel = torch.stack([ro[r0:r1].reshape(-1, 3), rd[r0:r1].reshape(-1, 3)])
+        r2, _, a2, _ = nk.render(H, W, focal, chunk=7000, rays=sel, use_viewdirs=True, ndc=False, near=2.0, far=6.0, **kw)
+        assert torch.equal(r2.reshape(r1 - r0, W, 3), rgb[r0:r1]) and torch.equal(a2.reshape(r1 - r0, W), acc[r0:r1])
