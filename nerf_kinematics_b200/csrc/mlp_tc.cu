@@ -278,6 +278,7 @@ mlp_tc_kernel(const __grid_constant__ TcPlan plan, const unsigned char* __restri
     // ============================ weight producer ============================
     if (lane == 0) {
       uint32_t slot = 0, phase = 0;
+      const uint64_t pol_w = l2_evict_last();
       for (long long tile = tile_begin; tile < tile_end; tile += 2) {
         for (int s = 0; s < plan.n_stages; ++s) {
           const TcStage& st = plan.st[s];
@@ -288,8 +289,8 @@ mlp_tc_kernel(const __grid_constant__ TcPlan plan, const unsigned char* __restri
               const uint32_t fb = smem_u32(bar_full + slot);
               if (dbg & 1) { mbar_arrive(fb); if (++slot == kFwdRing) { slot = 0; phase ^= 1; } continue; }
               mbar_expect_tx(fb, bytes);
-              bulk_g2s(smem_u32(ring + slot * kFwdSlotBytes), wpk + st.w_off + (size_t)kb * st.chunk_bytes + (size_t)h * bytes,
-                       bytes, fb);
+              bulk_g2s_hint(smem_u32(ring + slot * kFwdSlotBytes),
+                            wpk + st.w_off + (size_t)kb * st.chunk_bytes + (size_t)h * bytes, bytes, fb, pol_w);
               if (++slot == kFwdRing) { slot = 0; phase ^= 1; }
             }
           }
@@ -315,6 +316,7 @@ mlp_tc_kernel(const __grid_constant__ TcPlan plan, const unsigned char* __restri
     const uint32_t d_tmem = tmem_base + t * 256;
     const int n_steps = plan.n_steps;
     const size_t rec_stride = (size_t)plan.rec_blocks * kBlockBytes;
+    const uint64_t pol_rec = l2_evict_first();
     for (long long tile0 = tile_begin; tile0 < tile_end; tile0 += 2) {
       if (tile0 + t >= tile_end) {
         // trailing single tile: this issuer only keeps the ring's two-commit protocol going
@@ -332,7 +334,7 @@ mlp_tc_kernel(const __grid_constant__ TcPlan plan, const unsigned char* __restri
       mbar_wait(bar_enc_s, ph_enc);
       ph_enc ^= 1;
       if (rec && elect_one()) {
-        bulk_s2g(rec_t, act_s + enc_off, kBlockBytes);
+        bulk_s2g_hint(rec_t, act_s + enc_off, kBlockBytes, pol_rec);
         bulk_commit();
       }
       __syncwarp();
@@ -350,7 +352,7 @@ mlp_tc_kernel(const __grid_constant__ TcPlan plan, const unsigned char* __restri
             ph_encd ^= 1;
           }
           if (rec && elect_one()) {
-            bulk_s2g(rec_t + (size_t)e.w * kBlockBytes, act_s + (e.x & ~127u), kBlockBytes);
+            bulk_s2g_hint(rec_t + (size_t)e.w * kBlockBytes, act_s + (e.x & ~127u), kBlockBytes, pol_rec);
             bulk_commit();
           }
           __syncwarp();
