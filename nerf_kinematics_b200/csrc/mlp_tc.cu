@@ -6,18 +6,23 @@
 // models.py:233-256) for PAIRS of 128-point tiles.
 //
 // How (Blackwell execution model):
-//   * one CTA per SM, persistent over a contiguous range of tiles taken two at a time; 18 warps with fixed roles:
+//   * one CTA per SM, persistent over a contiguous range of tiles taken two at a time; 20 warps with fixed roles:
 //       warp 0     weight producer -- streams pre-swizzled 16-bit weight chunks (<= 256 N-rows x 32 K-elements, the
 //                                     exact UMMA SWIZZLE_64B K-major image) from L2 into a 3-slot shared-memory ring
 //                                     with bulk async copies (cp.async.bulk -> UBLKCP) completing on mbarriers;
-//       warp 1     MMA issuer      -- one thread issues tcgen05.mma (kind::f16, M=128, N<=256, K=16): every ring slot
-//                                     feeds BOTH tiles of the pair (A = that tile's activations in shared memory,
+//       warps 1-2  MMA issuers     -- one warp per tile walks a step program in warp-uniform control flow and issues
+//                                     tcgen05.mma (kind::f16, M=128, N<=256, K=16) from an elected lane: every ring
+//                                     slot feeds BOTH tiles of the pair (A = that tile's activations in shared memory,
 //                                     D = that tile's 256 fp32 TMEM columns), halving the weight traffic per point;
-//                                     tcgen05.commit releases ring slots / publishes the accumulators;
-//       warps 2-17 epilogue        -- 8 warps per tile (TMEM lane quarter x column-block parity), thread == row:
+//                                     tcgen05.commit releases ring slots / publishes the accumulators; in training
+//                                     the same warps bulk-store every operand block to the per-tile X record;
+//       warp 3     builds the step program, then idles;
+//       warps 4-19 epilogue        -- 8 warps per tile (TMEM lane quarter x column-block parity), thread == row:
 //                                     encode the tile's points (sin/cos by double-angle recurrence) straight into the
 //                                     swizzled A-operand layout, then per layer tcgen05.ld 64 accumulator columns,
-//                                     add bias, ReLU, pack to 16 bit and store them as the next layer's A operand.
+//                                     ReLU, pack to 16 bit and store them as the next layer's A operand (the bias is
+//                                     already in the accumulator: it rides in the MMA against the encoding block's
+//                                     constant-one channel).
 //                                     Each finished 64-column block is published on its own mbarrier and the
 //                                     accumulator is handed back as soon as the last tcgen05.ld has landed, so the
 //                                     next layer's MMAs start while the remaining blocks are still being converted.
