@@ -85,3 +85,24 @@ def test_bf16_pair_kernel_ragged_tile_counts(n_points):
         assert torch.isfinite(got).all()
         err = maxdiff(got, ref)
         assert err <= 2e-2 * max(1.0, float(ref.abs().max())), (kind, n_points, err)
+
+
+@pytest.mark.parametrize("cfg", [dict(use_viewdirs=False), dict(D=6, W=128), dict(D=8, W=256)])
+def test_bf16_biases_ride_in_the_mma_other_graphs_and_large_biases(cfg):
+    """The 16-bit kernel adds no bias in its epilogue: hidden-layer biases are element 63 of the encoding weights
+    (times the encoding block's constant-one channel) or one extra K=16 step.  Cover the graph without view
+    directions (output_linear head), a narrower and shallower trunk, and biases large enough
+    (x 20) that a dropped or misplaced one shows far above the 16-bit tolerance."""
+    pts, dirs = _pts(257, 3, 23)
+    sd = O.init_tf8x256_state(seed=9, **cfg)
+    sd = {k: (v * 20.0 if k.endswith(".bias") else v) for k, v in sd.items()}
+    uv = cfg.get("use_viewdirs", True)
+    ref = O.run_mlp("tf", sd, pts, dirs if uv else None, 10, 4)
+    m = nk.model_from_state_dict(sd).to(DEV)
+    m.precision = "bf16"
+    got = m.query(pts.to(DEV), dirs.to(DEV) if uv else None)
+    scale = float(ref.abs().max())
+    assert scale > 0.5, scale                   # the biases matter in this network
+    zero_b = {k: (torch.zeros_like(v) if k.endswith(".bias") else v) for k, v in sd.items()}
+    assert maxdiff(O.run_mlp("tf", zero_b, pts, dirs if uv else None, 10, 4), ref) > 0.1 * scale
+    assert maxdiff(got, ref) <= 1e-2 * max(1.0, scale), (maxdiff(got, ref), scale)
