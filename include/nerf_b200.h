@@ -28,7 +28,7 @@
 extern "C" {
 #endif
 
-#define NB_ABI_VERSION 2 /* 2: nb_render_rand gained philox_state, perturb, raw_noise_std */
+#define NB_ABI_VERSION 3 /* 2: nb_render_rand gained philox_state, perturb, raw_noise_std; 3: *_dev pose variants, nb_check_finite, NB_PREC_F16 */
 
 typedef enum nb_status {
   NB_OK = 0,
@@ -46,7 +46,10 @@ typedef enum nb_graph {
 
 typedef enum nb_precision {
   NB_PREC_FP32 = 0, /* FFMA path: fp32 operands and accumulation, layer by layer */
-  NB_PREC_BF16 = 1  /* fused tcgen05 path: bf16 operands, fp32 accumulation in TMEM */
+  NB_PREC_F16 = 1,  /* fused tcgen05 path: IEEE fp16 operands (kind::f16, saturating conversion at +-65504), fp32
+                       accumulation in TMEM.  north_star calls this the "bf16 tensor-core path"; fp16 runs at the same
+                       tcgen05 rate and is ~5x closer to the fp32 render */
+  NB_PREC_BF16 = 1  /* historical alias of NB_PREC_F16 (same value, same kernels) */
 } nb_precision;
 
 typedef struct nb_model nb_model_t;
@@ -92,6 +95,11 @@ int64_t nb_model_flops_per_point(const nb_model_t* m);
  * is given; out8 may be null.  n = number of scalars. */
 int nb_to8b(const float* x, const float* gt, int64_t n, unsigned char* out8, double* mse_accum, nb_stream_t stream);
 
+/* TF check_numerics (nerf/run_nerf.py:240-241: every output of render_rays is checked for NaN/Inf) as a device-side
+ * flag instead of a host synchronisation per tensor: *flag |= bit when x[0..n) holds a non-finite value.  `flag` is a
+ * DEVICE int the caller zeroes and reads back once per frame / step. */
+int nb_check_finite(const float* x, int64_t n, int* flag, int bit, nb_stream_t stream);
+
 /* ---------------------------------------------------------------- a1 ray generation
  * Replaces get_rays (TF run_nerf_helpers.py:123-130) / get_ray_bundle (PT nerf_helpers.py:67-110).
  * dir_cam = [(col-cx)/fx, -(row-cy)/fy, -1]; rays_d = sum_j dir_cam[j]*c2w[k][j]; rays_o = c2w[:,3].
@@ -100,6 +108,10 @@ int nb_to8b(const float* x, const float* gt, int64_t n, unsigned char* out8, dou
  */
 int nb_get_rays(int H, int W, float fx, float fy, float cx, float cy, const float* c2w34_host, int row0, int row1,
                 float* rays_o, float* rays_d, nb_stream_t stream);
+/* Same, with the 3x4 pose read from DEVICE memory when the kernel runs: a CUDA graph captured around the per-frame
+ * chain of render_path (TF run_nerf.py:339-375) then renders whatever pose was copied there before the replay. */
+int nb_get_rays_dev(int H, int W, float fx, float fy, float cx, float cy, const float* c2w34_dev, int row0, int row1,
+                    float* rays_o, float* rays_d, nb_stream_t stream);
 
 /* rays of selected pixels only.  The training loops draw N_rand pixel indices per step and build
  * the whole image's bundle to keep them (TF run_nerf.py:762-774 `coords[select_inds]`, PT train_nerf.py:240-253);
@@ -107,6 +119,8 @@ int nb_get_rays(int H, int W, float fx, float fy, float cx, float cy, const floa
  * `reshape(-1, 3)` on the [H, W, 3] bundle).  Bit-identical to gathering nb_get_rays' output. */
 int nb_get_rays_at(int H, int W, float fx, float fy, float cx, float cy, const float* c2w34_host,
                    const int64_t* pixel_index, int64_t n, float* rays_o, float* rays_d, nb_stream_t stream);
+int nb_get_rays_at_dev(int H, int W, float fx, float fy, float cx, float cy, const float* c2w34_dev,
+                       const int64_t* pixel_index, int64_t n, float* rays_o, float* rays_d, nb_stream_t stream);
 
 /* a3: ndc_rays (TF run_nerf_helpers.py:143-178 == PT nerf_helpers.py:170-197). In-place allowed.
  * focal / near are doubles because the reference evaluates -1/(W/(2*focal)) with Python (double) scalars

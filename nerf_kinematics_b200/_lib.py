@@ -57,6 +57,9 @@ SIGNATURES = {
     "nb_model_flops_per_point": (i64, [p]),
     "nb_get_rays": (i32, [i32, i32, f32, f32, f32, f32, C.POINTER(f32), i32, i32, p, p, p]),
     "nb_get_rays_at": (i32, [i32, i32, f32, f32, f32, f32, C.POINTER(f32), p, i64, p, p, p]),
+    "nb_get_rays_dev": (i32, [i32, i32, f32, f32, f32, f32, p, i32, i32, p, p, p]),
+    "nb_get_rays_at_dev": (i32, [i32, i32, f32, f32, f32, f32, p, p, i64, p, p, p]),
+    "nb_check_finite": (i32, [p, i64, p, i32, p]),
     "nb_to8b": (i32, [p, p, i64, p, p, p]),
     "nb_rng_advance": (i32, [p, p]),
     "nb_rng_fill": (i32, [p, i32, i32, f32, i64, i32, p, p]),
@@ -105,8 +108,8 @@ def _load():
             fn = getattr(lib, name)  # AttributeError here == the library does not export the header
             fn.restype = res
             fn.argtypes = args
-        if lib.nb_abi_version() != 2:
-            raise NerfB200Error("libnerf_b200.so ABI version %d, binding expects 2" % lib.nb_abi_version())
+        if lib.nb_abi_version() != 3:
+            raise NerfB200Error("libnerf_b200.so ABI version %d, binding expects 3" % lib.nb_abi_version())
         _lib = lib
         return lib
 

@@ -79,7 +79,7 @@ __device__ __forceinline__ double warp_sum_d(double v) {
 
 // torch.linspace(0, 1, n)[i] in fp32 (CPU kernel): step = fp32(1/(n-1)); the lower half counts up
 // from 0, the upper half counts down from 1 with a single rounding (fma).  Verified against
-// torch.linspace for n = 2..512 (tests/test_host_formulas.py restates it in numpy).
+// torch.linspace bit for bit on the GPU for S in {2, 33, 64, 128} (tests/test_gpu_stages.py, sample_coarse).
 __device__ __forceinline__ float linspace01(int i, int n) {
   if (n <= 1) return 0.0f;
   const float step = __fdiv_rn(1.0f, (float)(n - 1));

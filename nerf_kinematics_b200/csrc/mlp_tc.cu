@@ -292,7 +292,7 @@ mlp_tc_kernel(const __grid_constant__ TcPlan plan, const unsigned char* __restri
               const uint32_t bytes = (uint32_t)st.n_main * 64u;
               mbar_wait(smem_u32(bar_empty + slot), phase ^ 1);
               const uint32_t fb = smem_u32(bar_full + slot);
-              if (dbg & 1) { mbar_arrive(fb); if (++slot == kFwdRing) { slot = 0; phase ^= 1; } continue; }
+              if (NB_DBG(dbg & 1)) { mbar_arrive(fb); if (++slot == kFwdRing) { slot = 0; phase ^= 1; } continue; }
               mbar_expect_tx(fb, bytes);
               bulk_g2s_hint(smem_u32(ring + slot * kFwdSlotBytes),
                             wpk + st.w_off + (size_t)kb * st.chunk_bytes + (size_t)h * bytes, bytes, fb, pol_w);
@@ -458,7 +458,7 @@ mlp_tc_kernel(const __grid_constant__ TcPlan plan, const unsigned char* __restri
               tc_fence_before();
               mbar_arrive(smem_u32(bar_drain + t));
             }
-            if (dbg & 2) { fence_async_smem(); mbar_arrive(smem_u32(bar_act + 4 * t + j)); continue; }
+            if (NB_DBG(dbg & 2)) { fence_async_smem(); mbar_arrive(smem_u32(bar_act + 4 * t + j)); continue; }
             const uint32_t rp = smem_u32(act_t) + j * kBlockBytes + row * 128;
             if (st.alpha_dot) {
               const uint32_t wa = smem_u32(bias_s) + (plan.alpha_w_off + j * 64) * 4;
@@ -727,9 +727,13 @@ int tc_forward(const nb_model* m, const float* rays, int ray_stride, const float
   TcSrc src{rays, ray_stride, z_vals, n_samples > 0 ? n_samples : 1, pts, viewdirs, points_per_dir > 0 ? points_per_dir : 1};
   const int64_t n_tiles = ceil_div(n_points, kTileM);
   const int grid = (int)std::min<int64_t>(ceil_div(n_tiles, 2), sm_count());
-  // NB_FWD_DEBUG (timing experiments behind the numbers in DESIGN.md, results are then garbage): 1 = producer skips the
-  // weight loads, 2 = epilogue skips the conversion
+  // Timing experiments behind the numbers in DESIGN.md (results are then garbage) exist only in builds made with
+  // -DNB_TIMING_EXPERIMENTS: NB_FWD_DEBUG=1 producer skips the weight loads, 2 = epilogue skips the conversion
+#ifdef NB_TIMING_EXPERIMENTS
   static const int dbg = getenv("NB_FWD_DEBUG") ? atoi(getenv("NB_FWD_DEBUG")) : 0;
+#else
+  const int dbg = 0;
+#endif
   mlp_tc_kernel<<<grid, kThreadsTc, p->smem_bytes, stream>>>(p->plan, p->d_w, p->d_bias, src, (long long)n_points, raw, rec, dbg);
   NB_LAUNCHED();
   return NB_OK;

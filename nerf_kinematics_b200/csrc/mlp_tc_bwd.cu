@@ -415,7 +415,7 @@ mlp_tc_wgrad_kernel(const __grid_constant__ WgPlan plan, const __grid_constant__
         const unsigned char* xt = a.xrec + (size_t)tile * a.rec_blocks * kBlockBytes + hoff;
         mbar_wait(smem_u32(bar_empty + slot), phase ^ 1);
         const uint32_t fb = smem_u32(bar_full + slot);
-        if (a.dbg & 1) { mbar_arrive(fb); if (++slot == kWgStages) { slot = 0; phase ^= 1; } continue; }
+        if (NB_DBG(a.dbg & 1)) { mbar_arrive(fb); if (++slot == kWgStages) { slot = 0; phase ^= 1; } continue; }
         mbar_expect_tx(fb, (uint32_t)((u.m_load + u.n_x) * kHalfBytes));
         const uint32_t sbase = smem_u32(stages + slot * stage_bytes);
         for (int b = 0; b < u.m_load; ++b) bulk_g2s(sbase + b * kHalfBytes, dzt + (size_t)b * kBlockBytes, kHalfBytes, fb);
@@ -434,7 +434,7 @@ mlp_tc_wgrad_kernel(const __grid_constant__ WgPlan plan, const __grid_constant__
         tc_fence_after();
         const uint32_t sbase = smem_u32(stages + slot * stage_bytes);
         const uint32_t xb = sbase + u.m_blocks * kHalfBytes;
-        for (int mh = 0; mh < ((a.dbg & 2) ? 0 : u.m_blocks / 2); ++mh) {
+        for (int mh = 0; mh < (NB_DBG(a.dbg & 2) ? 0 : u.m_blocks / 2); ++mh) {
           const uint32_t ab = sbase + 2 * mh * kHalfBytes;
           const uint32_t d = tmem_base + mh * Ntot;
 #pragma unroll
@@ -455,7 +455,7 @@ mlp_tc_wgrad_kernel(const __grid_constant__ WgPlan plan, const __grid_constant__
     // [16w, 16w+16) of every stage; lane l owns the 16-byte chunk l of the 256-column row (block l>>3, chunk l&7).
     const int t = threadIdx.x - 64;
     const int rg = t >> 5, blk = lane >> 3, chunk = lane & 7;
-    const bool active = u.b_off >= 0 && blk < u.m_load && !(a.dbg & 4);
+    const bool active = u.b_off >= 0 && blk < u.m_load && !NB_DBG(a.dbg & 4);
     float cs[8];
 #pragma unroll
     for (int i = 0; i < 8; ++i) cs[i] = 0.0f;
@@ -872,10 +872,12 @@ int tc_backward(const nb_model* m, int64_t n_points, float* d_raw, void* ws, siz
   wa.rec_blocks = p->plan.rec_blocks;
   wa.drec_blocks = p->bw.drec_blocks;
   wg_assign(p->wg, L.n_tiles, sm_count(), wa.part0);
+#ifdef NB_TIMING_EXPERIMENTS
   {
     static const int dbg = getenv("NB_WG_DEBUG") ? atoi(getenv("NB_WG_DEBUG")) : 0;
     wa.dbg = dbg;
   }
+#endif
   const int wgrid = wa.part0[p->wg.n_units];
   mlp_tc_wgrad_kernel<<<wgrid, kThreadsWg, wg_smem_bytes(), stream>>>(p->wg, wa);
   NB_LAUNCHED();

@@ -55,9 +55,13 @@ __device__ __forceinline__ void pixel_ray(int col, int row, float fx, float fy, 
 // grid = (ceil(W / 256), rows): a block owns up to 256 consecutive pixels of one row, stages their 768 floats in shared
 // memory and writes them back as fully coalesced 128-byte warp stores (no 64-bit index division, no strided stores).
 __global__ void __launch_bounds__(256)
-get_rays_kernel(int W, float fx, float fy, float cx, float cy, Cam cam, int row0, float* __restrict__ ro,
-                float* __restrict__ rd) {
+get_rays_kernel(int W, float fx, float fy, float cx, float cy, Cam cam, const float* __restrict__ cam_dev, int row0,
+                float* __restrict__ ro, float* __restrict__ rd) {
   __shared__ float sd[768];
+  if (cam_dev != nullptr) {  // pose in device memory (a captured frame graph reads the pose of the replay, not of the capture)
+#pragma unroll
+    for (int k = 0; k < 12; ++k) cam.r[k] = __ldg(cam_dev + k);
+  }
   const int col0 = blockIdx.x * 256, col = col0 + threadIdx.x;
   const int row = row0 + blockIdx.y;
   const int npix = min(256, W - col0);
@@ -79,10 +83,15 @@ get_rays_kernel(int W, float fx, float fy, float cx, float cy, Cam cam, int row0
 
 // rays of selected pixels only (the training loop draws N_rand pixel indices per step and the
 // reference generates the whole image's rays to keep 1 024 of them, nerf-pytorch/train_nerf.py:240-253).
-__global__ void get_rays_at_kernel(int W, float fx, float fy, float cx, float cy, Cam cam, const int64_t* __restrict__ pix,
-                                   int64_t n, float* __restrict__ ro, float* __restrict__ rd) {
+__global__ void get_rays_at_kernel(int W, float fx, float fy, float cx, float cy, Cam cam, const float* __restrict__ cam_dev,
+                                   const int64_t* __restrict__ pix, int64_t n, float* __restrict__ ro,
+                                   float* __restrict__ rd) {
   const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
+  if (cam_dev != nullptr) {
+#pragma unroll
+    for (int k = 0; k < 12; ++k) cam.r[k] = __ldg(cam_dev + k);
+  }
   const int64_t p = pix[i];
   const int row = (int)(p / W), col = (int)(p - (int64_t)row * W);
   float d[3];
@@ -280,18 +289,47 @@ int nb_device_count(void) {
   return n;
 }
 
-int nb_get_rays(int H, int W, float fx, float fy, float cx, float cy, const float* c2w, int row0, int row1,
-                float* rays_o, float* rays_d, nb_stream_t stream) {
-  NB_REQUIRE(H > 0 && W > 0 && c2w, "nb_get_rays: bad arguments");
+static int get_rays_common(int H, int W, float fx, float fy, float cx, float cy, const float* c2w_host,
+                           const float* c2w_dev, int row0, int row1, float* rays_o, float* rays_d, nb_stream_t stream) {
+  NB_REQUIRE(H > 0 && W > 0 && (c2w_host || c2w_dev), "nb_get_rays: bad arguments");
   NB_REQUIRE(0 <= row0 && row0 <= row1 && row1 <= H, "nb_get_rays: rows [%d,%d) outside image height %d", row0, row1, H);
   int64_t n = (int64_t)(row1 - row0) * W;
   if (n == 0) return NB_OK;
   NB_REQUIRE(rays_o && rays_d, "nb_get_rays: null output");
-  Cam cam;
-  memcpy(cam.r, c2w, sizeof(cam.r));
+  Cam cam{};
+  if (c2w_host) memcpy(cam.r, c2w_host, sizeof(cam.r));
   NB_REQUIRE(row1 - row0 <= 65535, "nb_get_rays: more than 65535 rows in one call");
   dim3 grid((unsigned)ceil_div(W, 256), (unsigned)(row1 - row0));
-  get_rays_kernel<<<grid, 256, 0, as_stream(stream)>>>(W, fx, fy, cx, cy, cam, row0, rays_o, rays_d);
+  get_rays_kernel<<<grid, 256, 0, as_stream(stream)>>>(W, fx, fy, cx, cy, cam, c2w_dev, row0, rays_o, rays_d);
+  NB_LAUNCHED();
+  return NB_OK;
+}
+
+int nb_get_rays(int H, int W, float fx, float fy, float cx, float cy, const float* c2w, int row0, int row1,
+                float* rays_o, float* rays_d, nb_stream_t stream) {
+  NB_REQUIRE(c2w != nullptr, "nb_get_rays: null pose");
+  return get_rays_common(H, W, fx, fy, cx, cy, c2w, nullptr, row0, row1, rays_o, rays_d, stream);
+}
+
+int nb_get_rays_dev(int H, int W, float fx, float fy, float cx, float cy, const float* c2w34_dev, int row0, int row1,
+                    float* rays_o, float* rays_d, nb_stream_t stream) {
+  NB_REQUIRE(c2w34_dev != nullptr, "nb_get_rays_dev: null pose");
+  return get_rays_common(H, W, fx, fy, cx, cy, nullptr, c2w34_dev, row0, row1, rays_o, rays_d, stream);
+}
+
+// TF check_numerics (nerf/run_nerf.py:240-241) without a host round trip per tensor: flag |= 1 when any element is NaN/Inf
+__global__ void check_finite_kernel(const float* __restrict__ x, int64_t n, int* __restrict__ flag, int bit) {
+  bool bad = false;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
+    bad |= !isfinite(x[i]);
+  if (__any_sync(0xffffffffu, bad) && (threadIdx.x & 31) == 0) atomicOr(flag, bit);
+}
+
+int nb_check_finite(const float* x, int64_t n, int* flag, int bit, nb_stream_t stream) {
+  NB_REQUIRE(n >= 0 && flag != nullptr && (n == 0 || x != nullptr), "nb_check_finite: bad arguments");
+  if (n == 0) return NB_OK;
+  const unsigned grid = (unsigned)std::min<int64_t>(ceil_div(n, 256), (int64_t)sm_count() * 8);
+  check_finite_kernel<<<grid, 256, 0, as_stream(stream)>>>(x, n, flag, bit);
   NB_LAUNCHED();
   return NB_OK;
 }
@@ -307,17 +345,30 @@ int nb_to8b(const float* x, const float* gt, int64_t n, unsigned char* out8, dou
   return NB_OK;
 }
 
-int nb_get_rays_at(int H, int W, float fx, float fy, float cx, float cy, const float* c2w, const int64_t* pixel_index,
-                   int64_t n, float* rays_o, float* rays_d, nb_stream_t stream) {
-  NB_REQUIRE(H > 0 && W > 0 && c2w && n >= 0, "nb_get_rays_at: bad arguments");
+static int get_rays_at_common(int H, int W, float fx, float fy, float cx, float cy, const float* c2w_host,
+                              const float* c2w_dev, const int64_t* pixel_index, int64_t n, float* rays_o, float* rays_d,
+                              nb_stream_t stream) {
+  NB_REQUIRE(H > 0 && W > 0 && (c2w_host || c2w_dev) && n >= 0, "nb_get_rays_at: bad arguments");
   if (n == 0) return NB_OK;
   NB_REQUIRE(pixel_index && rays_o && rays_d, "nb_get_rays_at: null pointer");
-  Cam cam;
-  memcpy(cam.r, c2w, sizeof(cam.r));
-  get_rays_at_kernel<<<(unsigned)ceil_div(n, 256), 256, 0, as_stream(stream)>>>(W, fx, fy, cx, cy, cam, pixel_index, n, rays_o,
-                                                                           rays_d);
+  Cam cam{};
+  if (c2w_host) memcpy(cam.r, c2w_host, sizeof(cam.r));
+  get_rays_at_kernel<<<(unsigned)ceil_div(n, 256), 256, 0, as_stream(stream)>>>(W, fx, fy, cx, cy, cam, c2w_dev, pixel_index, n,
+                                                                           rays_o, rays_d);
   NB_LAUNCHED();
   return NB_OK;
+}
+
+int nb_get_rays_at(int H, int W, float fx, float fy, float cx, float cy, const float* c2w, const int64_t* pixel_index,
+                   int64_t n, float* rays_o, float* rays_d, nb_stream_t stream) {
+  NB_REQUIRE(c2w != nullptr, "nb_get_rays_at: null pose");
+  return get_rays_at_common(H, W, fx, fy, cx, cy, c2w, nullptr, pixel_index, n, rays_o, rays_d, stream);
+}
+
+int nb_get_rays_at_dev(int H, int W, float fx, float fy, float cx, float cy, const float* c2w34_dev,
+                       const int64_t* pixel_index, int64_t n, float* rays_o, float* rays_d, nb_stream_t stream) {
+  NB_REQUIRE(c2w34_dev != nullptr, "nb_get_rays_at_dev: null pose");
+  return get_rays_at_common(H, W, fx, fy, cx, cy, nullptr, c2w34_dev, pixel_index, n, rays_o, rays_d, stream);
 }
 
 static NdcScale make_ndc_scale(int H, int W, double focal, double near) {

@@ -7,6 +7,14 @@
 
 #include "model.h"
 
+// Kernel-side timing hooks (skip loads / MMAs / conversions) exist only in -DNB_TIMING_EXPERIMENTS builds; a release
+// build cannot be switched into returning garbage by an environment variable.
+#ifdef NB_TIMING_EXPERIMENTS
+#define NB_DBG(x) (x)
+#else
+#define NB_DBG(x) false
+#endif
+
 namespace nb {
 
 constexpr int kMaxStages = 14;

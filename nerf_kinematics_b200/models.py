@@ -24,14 +24,16 @@ from . import _lib
 from ._lib import check, lib
 
 GRAPH_NERF, GRAPH_FLEXIBLE = 0, 1
-_PREC = {"fp32": 0, "bf16": 1, 0: 0, 1: 1}
+# "fp16" is what the tensor-core path computes in (IEEE half operands, fp32 accumulation); "bf16" is kept as an alias
+# because north_star / the reference-facing kwargs call it the "bf16 tensor-core path".
+_PREC = {"fp32": 0, "fp16": 1, "f16": 1, "bf16": 1, 0: 0, 1: 1}
 
 
 def precision_id(p) -> int:
     try:
         return _PREC[p]
     except KeyError:
-        raise ValueError("precision must be 'fp32' or 'bf16', got %r" % (p,))
+        raise ValueError("precision must be 'fp32' or 'fp16' (alias 'bf16'), got %r" % (p,))
 
 
 class KernelMLP(nn.Module):
@@ -159,12 +161,13 @@ class KernelMLP(nn.Module):
 
     # -- evaluation ----------------------------------------------------------------------------
     def query(self, pts, viewdirs=None, precision=None):
-        """network_query_fn semantics (nerf/run_nerf.py:30-45): pts [..., S, 3], viewdirs [..., 3] -> raw [..., S, 4]."""
+        """network_query_fn semantics (nerf/run_nerf.py:30-45): pts [..., S, 3], viewdirs [..., 3] -> raw [..., S, 4].
+        A 2-D pts [N, 3] is N independent points: viewdirs must then be [N, 3] (one direction per point)."""
         from .ops import _f32, _optptr, _ptr, _stream
         h, prec = self.prepare(precision)
         p = _f32(pts, "pts")
         lead = p.shape[:-1]
-        S = p.shape[-2] if p.dim() >= 2 else 1
+        S = p.shape[-2] if p.dim() >= 3 else 1
         p2 = p.reshape(-1, 3)
         vd = None
         if self.use_viewdirs:
@@ -172,7 +175,8 @@ class KernelMLP(nn.Module):
                 raise ValueError("this model was built with use_viewdirs=True")
             vd = _f32(viewdirs, "viewdirs").reshape(-1, 3)
             if vd.shape[0] * S != p2.shape[0]:
-                raise ValueError("viewdirs [%d,3] do not match pts %s" % (vd.shape[0], tuple(pts.shape)))
+                raise ValueError("viewdirs [%d,3] do not match pts %s: pass one direction per ray for pts "
+                                 "[N_rays, S, 3], one per point for pts [N, 3]" % (vd.shape[0], tuple(pts.shape)))
         n = p2.shape[0]
         raw = torch.empty((n, 4), dtype=torch.float32, device=p.device)
         with torch.cuda.device(p.device):
@@ -218,10 +222,14 @@ class NeRF(KernelMLP):
         self.n_freq_xyz, self.n_freq_dir = (input_ch - 3) // 6, ((input_ch_views - 3) // 6 if use_viewdirs else 0)
         self._create_handle(GRAPH_NERF, D, W, self.n_freq_xyz, self.n_freq_dir, use_viewdirs, skip)
 
-    # Keras get_weights() order: [kernel[in,out], bias] per layer in creation order (nerf/run_nerf.py:835-843)
+    # Keras get_weights() order (np.save(net.get_weights()), nerf/run_nerf.py:835-843): [kernel[in,out], bias] per layer,
+    # layers of a functional Model sorted by graph depth -- the trunk, then bottleneck, views, rgb, and alpha LAST
+    # (alpha's Dense(1) feeds only the final concat, so it sits at the same depth as rgb and after it): index 2D =
+    # bottleneck [W,256], 2D+2 = views [256+27, W/2], 2D+4 = rgb [W/2,3], 2D+6 = alpha [W,1] -- the layout of the
+    # official model_200000.npy files and of the well-known load_weights_from_keras converters.
     def keras_layer_names(self):
         names = ["pts_linears.%d" % i for i in range(self.D)]
-        names += ["alpha_linear", "bottleneck_linear", "views_linears.0", "rgb_linear"] if self.use_viewdirs \
+        names += ["bottleneck_linear", "views_linears.0", "rgb_linear", "alpha_linear"] if self.use_viewdirs \
             else ["output_linear"]
         return names
 
@@ -238,9 +246,16 @@ class NeRF(KernelMLP):
         if len(weights) != 2 * len(names):
             raise ValueError("expected %d arrays, got %d" % (2 * len(names), len(weights)))
         sd = {}
+        own = self.state_dict()
         for i, n in enumerate(names):
-            sd[n + ".weight"] = torch.as_tensor(weights[2 * i]).t().contiguous()
-            sd[n + ".bias"] = torch.as_tensor(weights[2 * i + 1])
+            w, b = torch.as_tensor(weights[2 * i]), torch.as_tensor(weights[2 * i + 1])
+            if tuple(w.shape) != tuple(own[n + ".weight"].shape[::-1]) or tuple(b.shape) != tuple(own[n + ".bias"].shape):
+                raise ValueError("weights[%d] / [%d] have shapes %s / %s; %s expects kernel %s, bias %s (Keras order: "
+                                 "trunk, bottleneck, views, rgb, alpha)" % (2 * i, 2 * i + 1, tuple(w.shape), tuple(b.shape),
+                                                                            n, tuple(own[n + ".weight"].shape[::-1]),
+                                                                            tuple(own[n + ".bias"].shape)))
+            sd[n + ".weight"] = w.t().contiguous()
+            sd[n + ".bias"] = b
         self.load_state_dict(sd)
 
 

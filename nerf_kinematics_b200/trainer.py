@@ -57,13 +57,17 @@ class TrainStep:
         off_f = _round_up(nc, 64)
         self.bucket = torch.zeros((off_f + nf,), dtype=torch.float32, device=dev)
         self.gc, self.gf = self.bucket[:nc], (self.bucket[off_f:off_f + nf] if nf else None)
+        # The optimizer sees the parameters in REGISTRATION order, coarse then fine, exactly like the reference's
+        # `list(model_coarse.parameters()) + list(model_fine.parameters())` (train_nerf.py:165-167): optimizer state
+        # dicts index parameters by position, so this is what makes a shipped `optimizer_state_dict` line up.  The flat
+        # buffers keep the native order; aliasing goes by view, not by position.
         params = []
         for m, gflat in ((self.mc, self.gc), (self.mf, self.gf)):
             if m is None:
                 continue
             for p, gv in m.grad_views(gflat):
                 p.grad = gv
-                params.append(p)
+            params += list(m.parameters())
         self.params = params
         self.opt = optimizer if optimizer is not None else torch.optim.Adam(params, lr=lrate, betas=self.betas, eps=eps)
         self.global_step = 0

@@ -1,8 +1,9 @@
-"""Import the reference's own PyTorch implementation (read-only, /root/reference).
+"""Import the reference's own PyTorch implementation, unmodified.
 
-TEST INFRASTRUCTURE ONLY.  Works only in the build container (the GPU box has no
-/root/reference); used by oracle/make_golden.py to generate tests/golden/*.npz and by
-tests that are skipped when the reference tree is absent.
+TEST / BASELINE INFRASTRUCTURE ONLY.  The package is imported from /root/reference when that exists (the build
+container) and otherwise from oracle/_ref/, the verbatim copy staged by oracle/build_ref.py (git-ignored; it
+travels to the GPU box with the snapshot).  Used by oracle/make_golden.py to generate tests/golden/*.npz, by the
+tests that pin the oracle, and by bench.py's reference arm / cpu_baseline leg (oracle/ref_arm.py).
 
 Two third-party modules the reference imports are absent from this image and are shimmed:
   * torchsearchsorted (nerf-pytorch/requirements.txt:9, unpinned git HEAD) ->
@@ -15,7 +16,17 @@ import types
 
 import torch
 
-REF_ROOT = os.environ.get("NERF_REFERENCE_ROOT", "/root/reference")
+_HERE = os.path.dirname(os.path.abspath(__file__))
+
+
+def _find_root():
+    for c in (os.environ.get("NERF_REFERENCE_ROOT"), "/root/reference", os.path.join(_HERE, "_ref")):
+        if c and os.path.isdir(os.path.join(c, "nerf-pytorch", "nerf")):
+            return c
+    return "/root/reference"
+
+
+REF_ROOT = _find_root()
 REF_PT = os.path.join(REF_ROOT, "nerf-pytorch")
 
 

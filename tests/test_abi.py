@@ -27,7 +27,7 @@ def test_library_exports_every_declared_symbol():
     for n in names:
         assert hasattr(lib, n), "libnerf_b200.so does not export %s" % n
     assert sorted(_lib.SIGNATURES) == names, set(names) ^ set(_lib.SIGNATURES)
-    assert _lib.lib().nb_abi_version() == 2
+    assert _lib.lib().nb_abi_version() == 3
 
 
 def test_no_torch_types_in_abi():
@@ -58,6 +58,33 @@ def test_model_layouts_match_reference_state_dicts():
     tf2.set_weights(w)
     for a, b in zip(tf.state_dict().values(), tf2.state_dict().values()):
         assert torch.equal(a, b)
+
+
+def test_keras_weight_list_order_matches_real_npy_files():
+    """A Keras functional Model lists layers by graph depth: trunk, bottleneck, views, rgb, and alpha LAST (the
+    official model_200000.npy / model_fine_*.npy layout read by the load_weights_from_keras converters): index
+    2D = [W,256], 2D+2 = [256+27, W/2], 2D+4 = [W/2,3], 2D+6 = [W,1]."""
+    D, W = 8, 256
+    tf = nk.NeRF(D=D, W=W)
+    w = tf.get_weights()
+    shapes = [tuple(a.shape) for a in w]
+    assert shapes[2 * D] == (W, 256) and shapes[2 * D + 1] == (256,)
+    assert shapes[2 * D + 2] == (256 + 27, W // 2) and shapes[2 * D + 4] == (W // 2, 3)
+    assert shapes[2 * D + 6] == (W, 1) and shapes[2 * D + 7] == (1,)
+    # a list in the real file's shapes loads; alpha lands on alpha_linear
+    import numpy as np
+    rs = np.random.RandomState(0)
+    real = [rs.randn(*s).astype(np.float32) for s in shapes]
+    tf.set_weights(real)
+    assert torch.equal(tf.alpha_linear.weight.detach().cpu(), torch.from_numpy(real[2 * D + 6]).t())
+    assert torch.equal(tf.bottleneck_linear.bias.detach().cpu(), torch.from_numpy(real[2 * D + 1]))
+    # the old (wrong) order [alpha, bottleneck, views, rgb] is rejected instead of silently mis-assigned
+    wrong = real[:2 * D] + real[2 * D + 6:] + real[2 * D:2 * D + 6]
+    with pytest.raises(ValueError):
+        tf.set_weights(wrong)
+    # without view directions: trunk + output_linear
+    nv = nk.NeRF(use_viewdirs=False, input_ch_views=3)
+    assert [tuple(a.shape) for a in nv.get_weights()][-2:] == [(W, 4), (4,)]
 
 
 def test_flexible_with_active_skip_is_rejected_like_the_reference_crash():
