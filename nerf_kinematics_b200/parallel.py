@@ -42,6 +42,14 @@ def render_rows(H, W, K, c2w, rank, world, chunk=1024 * 32, near=0.0, far=1.0, n
                 **render_kwargs):
     """This rank's row block of render(H, W, K, c2w=...) -> dict of [rows, W, ...] tensors.  No collective."""
     r0, r1 = row_block(H, rank, world)
+    from .run_nerf import _frame_renderer
+    fr = _frame_renderer(int(H), int(W), K, chunk, ndc, near, far, use_viewdirs, render_kwargs, rows=(r0, r1))
+    if fr is not None:   # inference form: the row block is one captured CUDA graph (frame.FrameRenderer)
+        out = fr.render(c2w, clone=not render_kwargs.get("_static_outputs", False))
+        ret = {"rgb_map": out["rgb"], "disp_map": out["disp"], "acc_map": out["acc"]}
+        ret.update({k: out[k] for k in ("rgb0", "disp0", "acc0", "z_std") if k in out})
+        return ret, (r0, r1)
+    render_kwargs = {k: v for k, v in render_kwargs.items() if k != "_static_outputs"}
     ro, rd = ops.get_rays(H, W, K, c2w, row0=r0, row1=r1)
     fx, _, _, _ = ops.intrinsics(H, W, K)
     packed = ops.make_ray_batch(ro, rd, near, far, use_viewdirs=use_viewdirs, ndc=ndc, H=H, W=W, focal=fx)

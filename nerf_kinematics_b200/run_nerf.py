@@ -16,7 +16,8 @@ import time
 import numpy as np
 import torch
 
-from . import ops
+from . import _lib, ops
+from .frame import FrameRenderer
 from .models import NeRF
 from .nerf_helpers import get_embedder, to8b
 from .render_core import render_chunk
@@ -40,10 +41,18 @@ def render_rays(ray_batch, network_fn, network_query_fn, N_samples, retraw=False
         ret["raw"] = out["raw"]
     if N_importance > 0:
         ret["rgb0"], ret["disp0"], ret["acc0"], ret["z_std"] = out["rgb0"], out["disp0"], out["acc0"], out["z_std"]
-    if check_numerics:
-        for k, v in ret.items():
-            if not torch.isfinite(v).all():
-                raise FloatingPointError("output %s : Tensor had NaN or Inf values" % k)
+    if check_numerics:  # TF check_numerics (run_nerf.py:240-241): one device flag for all outputs, read back once
+        flag = torch.zeros(1, dtype=torch.int32, device=ray_batch.device)
+        keys = list(ret)
+        with torch.cuda.device(ray_batch.device):
+            for bit, k in enumerate(keys):
+                v = ret[k].contiguous()
+                _lib.check(_lib.lib().nb_check_finite(ops._ptr(v), v.numel(), ops._ptr(flag), 1 << bit, ops._stream()),
+                           "nb_check_finite")
+        bits = int(flag.item())
+        if bits:
+            bad = [k for b, k in enumerate(keys) if bits & (1 << b)]
+            raise FloatingPointError("output %s : Tensor had NaN or Inf values" % ", ".join(bad))
     return ret
 
 
@@ -62,12 +71,58 @@ def _focal_scalar(K):
     return fx
 
 
+_FRAME_CACHE_MAX = 4
+
+
+def _frame_renderer(H, W, focal, chunk, ndc, near, far, use_viewdirs, kwargs, rows=None):
+    """A cached FrameRenderer when this render() call is the plain per-pose inference form (pose given, no gradient
+    wanted, no random inputs, no retraw): the whole frame is then one CUDA-graph replay.  None otherwise."""
+    fn = kwargs.get("network_fn")
+    if fn is None or not hasattr(fn, "prepare"):
+        return None
+    if kwargs.get("retraw") or kwargs.get("rnd") or kwargs.get("perturb") or (kwargs.get("raw_noise_std") or 0.0) > 0.0:
+        return None
+    if isinstance(near, torch.Tensor) or isinstance(far, torch.Tensor):
+        return None
+    fine = kwargs.get("network_fine")
+    nets = [fn] + ([fine] if fine is not None else [])
+    if torch.is_grad_enabled() and any(p.requires_grad for m in nets for p in m.parameters()):
+        return None
+    fx, fy, cx, cy = ops.intrinsics(H, W, focal)
+    r0, r1 = rows if rows is not None else (0, H)
+    key = (H, W, fx, fy, cx, cy, int(chunk), bool(ndc), float(near), float(far), bool(use_viewdirs), id(fine),
+           int(kwargs.get("N_samples")), int(kwargs.get("N_importance", 0)), bool(kwargs.get("lindisp", False)),
+           bool(kwargs.get("white_bkgd", False)), kwargs.get("precision") or fn.precision,
+           bool(kwargs.get("check_numerics", False)), r0, r1)
+    cache = fn.__dict__.setdefault("_frame_cache", {})
+    fr = cache.get(key)
+    if fr is None:
+        if len(cache) >= _FRAME_CACHE_MAX:
+            cache.pop(next(iter(cache)))
+        fr = FrameRenderer(H, W, focal, fn, fine, chunk=chunk, row0=r0, row1=r1, near=near, far=far, ndc=ndc,
+                           use_viewdirs=use_viewdirs, N_samples=kwargs["N_samples"],
+                           N_importance=kwargs.get("N_importance", 0), lindisp=kwargs.get("lindisp", False),
+                           white_bkgd=kwargs.get("white_bkgd", False), precision=kwargs.get("precision"),
+                           check_numerics=kwargs.get("check_numerics", False))
+        cache[key] = fr
+    return fr
+
+
 def render(H, W, focal, chunk=1024 * 32, rays=None, c2w=None, ndc=True, near=0.0, far=1.0, use_viewdirs=False,
-           c2w_staticcam=None, **kwargs):
-    """run_nerf.py:260-336 -> [rgb_map, disp_map, acc_map, extras].  `focal` may be a 3x3 K."""
+           c2w_staticcam=None, _static_outputs=False, _rows=None, **kwargs):
+    """run_nerf.py:260-336 -> [rgb_map, disp_map, acc_map, extras].  `focal` may be a 3x3 K.
+    With a pose and inference options the frame runs as one captured CUDA graph (frame.FrameRenderer); results are
+    identical to the chunk-by-chunk path (same kernels, same order per ray)."""
     H, W = int(H), int(W)
+    if c2w is not None and c2w_staticcam is None:
+        fr = _frame_renderer(H, W, focal, chunk, ndc, near, far, use_viewdirs, kwargs, rows=_rows)
+        if fr is not None:
+            out = fr.render(c2w, clone=not _static_outputs)
+            extras = {k: out[k] for k in ("rgb0", "disp0", "acc0", "z_std") if k in out}
+            return [out["rgb"], out["disp"], out["acc"], extras]
     if c2w is not None:
-        rays_o, rays_d = ops.get_rays(H, W, focal, c2w)
+        r0, r1 = _rows if _rows is not None else (0, H)   # a rank's row block (multi-GPU render: SURVEY 8e)
+        rays_o, rays_d = ops.get_rays(H, W, focal, c2w, row0=r0, row1=r1)
     else:
         rays_o, rays_d = rays[0], rays[1]
     viewdir_src = None
@@ -89,8 +144,11 @@ def render(H, W, focal, chunk=1024 * 32, rays=None, c2w=None, ndc=True, near=0.0
     return ret_list + [ret_dict]
 
 
-def render_path(render_poses, hwf, chunk, render_kwargs, gt_imgs=None, savedir=None, render_factor=0, verbose=False):
-    """run_nerf.py:339-375 -> (rgbs [M,H,W,3], disps [M,H,W]) as numpy arrays."""
+def render_path(render_poses, hwf, chunk, render_kwargs, gt_imgs=None, savedir=None, render_factor=0, verbose=False,
+                row_block=None):
+    """run_nerf.py:339-375 -> (rgbs [M,H,W,3], disps [M,H,W]) as numpy arrays.
+    row_block=(rank, world) (extension): this process renders only its contiguous block of image rows of
+    every pose and returns [M, rows, W, ...]; ranks share nothing, there is no collective."""
     H, W, focal = hwf
     if render_factor != 0:
         H, W = H // render_factor, W // render_factor
@@ -98,7 +156,13 @@ def render_path(render_poses, hwf, chunk, render_kwargs, gt_imgs=None, savedir=N
     # the reference converts every frame with .numpy() as soon as it is rendered (run_nerf.py:358),
     # which serialises host and device.  Here each frame is copied into pinned host memory asynchronously (the next
     # pose renders while the previous one drains), to8b / PSNR run on the device, and the host waits once at the end.
-    poses_list = [torch.as_tensor(c)[:3, :4] for c in render_poses]
+    rows = None
+    if row_block is not None:
+        rank, world = row_block
+        base, rem = divmod(int(H), int(world))
+        r0 = rank * base + min(rank, rem)
+        rows = (r0, r0 + base + (1 if rank < rem else 0))
+    poses_list = [(c if isinstance(c, torch.Tensor) else torch.as_tensor(np.asarray(c)))[:3, :4] for c in render_poses]
     M = len(poses_list)
     rgbs_h = disps_h = u8_h = None
     psnrs = []
@@ -108,7 +172,10 @@ def render_path(render_poses, hwf, chunk, render_kwargs, gt_imgs=None, savedir=N
             if verbose:
                 print(i, time.time() - t)
                 t = time.time()
-            rgb, disp, acc, _ = render(H, W, focal, chunk=chunk, c2w=c2w, **render_kwargs)
+            # _static_outputs: the frame's buffers are copied to the host right below, before the next replay on the
+            # same stream overwrites them -- no per-frame clone
+            rgb, disp, acc, _ = render(H, W, focal, chunk=chunk, c2w=c2w, _static_outputs=True, _rows=rows,
+                                       **render_kwargs)
             if rgbs_h is None:
                 pin = rgb.is_cuda
                 rgbs_h = torch.empty((M,) + tuple(rgb.shape), dtype=torch.float32, pin_memory=pin)
@@ -120,6 +187,8 @@ def render_path(render_poses, hwf, chunk, render_kwargs, gt_imgs=None, savedir=N
             want_psnr = gt_imgs is not None and render_factor == 0 and verbose
             if want_psnr or savedir is not None:
                 gt = torch.as_tensor(np.asarray(gt_imgs[i]), dtype=torch.float32) if want_psnr else None
+                if gt is not None and rows is not None:
+                    gt = gt[rows[0]:rows[1]]
                 u8, psnr = ops.to8b_psnr(rgb, gt, want_u8=savedir is not None)
                 if u8 is not None:
                     u8_h[i].copy_(u8, non_blocking=True)
