@@ -41,16 +41,27 @@ def get_rays(H: int, W: int, K, c2w, row0: int = 0, row1: int = None, device=Non
     if row1 is None:
         row1 = H
     fx, fy, cx, cy = intrinsics(H, W, K)
-    c2w_h = torch.as_tensor(c2w, dtype=torch.float32).detach().cpu()[:3, :4].contiguous()
+    on_dev = isinstance(c2w, torch.Tensor) and c2w.is_cuda
     if device is None:
-        device = c2w.device if isinstance(c2w, torch.Tensor) and c2w.is_cuda else torch.device("cuda")
+        device = c2w.device if on_dev else torch.device("cuda")
     with torch.cuda.device(device):
-        n = (row1 - row0) * W
         ro = torch.empty((row1 - row0, W, 3), dtype=torch.float32, device=device)
         rd = torch.empty_like(ro)
-        arr = (C.c_float * 12)(*c2w_h.reshape(-1).tolist())
-        check(lib().nb_get_rays(H, W, fx, fy, cx, cy, arr, row0, row1, _ptr(ro), _ptr(rd), _stream()), "nb_get_rays")
+        if on_dev:   # pose already on the device: the kernel reads it there, no device-to-host synchronisation
+            pose = c2w.detach()[:3, :4].to(device=device, dtype=torch.float32).contiguous()
+            check(lib().nb_get_rays_dev(H, W, fx, fy, cx, cy, _ptr(pose), row0, row1, _ptr(ro), _ptr(rd), _stream()),
+                  "nb_get_rays_dev")
+        else:
+            arr = (C.c_float * 12)(*_host_pose(c2w))
+            check(lib().nb_get_rays(H, W, fx, fy, cx, cy, arr, row0, row1, _ptr(ro), _ptr(rd), _stream()), "nb_get_rays")
     return ro, rd
+
+
+def _host_pose(c2w):
+    """12 floats (3x4 row-major) from a host pose (numpy array, nested list or CPU tensor)."""
+    import numpy as np
+    a = c2w.detach().numpy() if isinstance(c2w, torch.Tensor) else np.asarray(c2w)
+    return [float(v) for v in np.asarray(a, dtype=np.float32)[:3, :4].reshape(-1)]
 
 
 def get_rays_at(H: int, W: int, K, c2w, pixel_index, device=None):
@@ -58,16 +69,21 @@ def get_rays_at(H: int, W: int, K, c2w, pixel_index, device=None):
     `get_rays(H, W, K, c2w)` flattened with reshape(-1, 3) and indexed (train_nerf.py:240-253)."""
     _lib.require_cuda()
     fx, fy, cx, cy = intrinsics(H, W, K)
-    c2w_h = torch.as_tensor(c2w, dtype=torch.float32).detach().cpu()[:3, :4].contiguous()
+    on_dev = isinstance(c2w, torch.Tensor) and c2w.is_cuda
     if device is None:
         device = pixel_index.device if isinstance(pixel_index, torch.Tensor) and pixel_index.is_cuda else torch.device("cuda")
     idx = torch.as_tensor(pixel_index, dtype=torch.int64).to(device).contiguous()
     with torch.cuda.device(device):
         ro = torch.empty((idx.numel(), 3), dtype=torch.float32, device=device)
         rd = torch.empty_like(ro)
-        arr = (C.c_float * 12)(*c2w_h.reshape(-1).tolist())
-        check(lib().nb_get_rays_at(H, W, fx, fy, cx, cy, arr, _ptr(idx), idx.numel(), _ptr(ro), _ptr(rd), _stream()),
-              "nb_get_rays_at")
+        if on_dev:
+            pose = c2w.detach()[:3, :4].to(device=device, dtype=torch.float32).contiguous()
+            check(lib().nb_get_rays_at_dev(H, W, fx, fy, cx, cy, _ptr(pose), _ptr(idx), idx.numel(), _ptr(ro), _ptr(rd),
+                                           _stream()), "nb_get_rays_at_dev")
+        else:
+            arr = (C.c_float * 12)(*_host_pose(c2w))
+            check(lib().nb_get_rays_at(H, W, fx, fy, cx, cy, arr, _ptr(idx), idx.numel(), _ptr(ro), _ptr(rd), _stream()),
+                  "nb_get_rays_at")
     return ro, rd
 
 

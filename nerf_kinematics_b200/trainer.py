@@ -71,6 +71,7 @@ class TrainStep:
         self.params = params
         self.opt = optimizer if optimizer is not None else torch.optim.Adam(params, lr=lrate, betas=self.betas, eps=eps)
         self.global_step = 0
+        self.lr_offset = 0   # schedule index = global_step + lr_offset (train_nerf.py's loop lags one iteration, resumes shift it)
         self.loss_buf = torch.zeros((2,), dtype=torch.float32, device=dev)
         # jitter / inverse-CDF uniforms / sigma noise are drawn inside the kernels (Philox, counter =
         # ray, sample, input, step) unless the caller injects arrays; {seed, step} lives on the device so that a
@@ -132,7 +133,7 @@ class TrainStep:
     def learning_rate(self, step_index):
         """lr used by iteration `step_index` (0-based): lr0 * decay_rate ** (i / decay_steps) (run_nerf.py:705-709,
         train_nerf.py:292-297 set it after iteration i-1 for iteration i)."""
-        return self.lrate * (self.decay_rate ** (step_index / self.decay_steps))
+        return self.lrate * (self.decay_rate ** (max(step_index + self.lr_offset, 0) / self.decay_steps))
 
     # ------------------------------------------------------------------ device side of one iteration
     def _workspace(self, n, stride, cfg, hc, hf, dev):
