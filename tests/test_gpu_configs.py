@@ -1,0 +1,139 @@
+"""GPU: the BASELINE.json configurations that had never run at shape.
+
+configs[2]  robot wheel, 1280 x 720: poses.txt -> unmodified parser_instant_ngp.py -> transforms_test_video.json (committed
+            fixture of the parser's output) -> load_transforms -> render with the 3x3 K (fl_x 674.42 != fl_y 649.46), NDC,
+            the shipped wheel_robot6 checkpoint.  fp32 parity against the oracle on a strided subset of rows, the
+            tensor-core path on the full 921 600-ray frame through properties + row-block tiling.
+configs[3]  fern LLFF, 504 x 378: NDC + use_viewdirs + Lx = 10 + 8x256, a pose of the 120-view render_path_spiral, and a
+            training step at N_rand = 4096 with raw_noise_std = 1 (paper_configs/llff_config.txt:18-20).
+configs[4]  ray-batch form (rays handed in, no image): the captured chunk chain equals the chunk-by-chunk call.
+"""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from conftest import GOLD, load_golden, maxdiff
+from oracle import nerf_oracle as O
+
+pytestmark = pytest.mark.gpu
+
+import nerf_kinematics_b200 as nk  # noqa: E402
+from nerf_kinematics_b200 import ops, parallel  # noqa: E402
+from nerf_kinematics_b200.frame import FrameRenderer  # noqa: E402
+from nerf_kinematics_b200.poses import load_transforms, render_path_spiral  # noqa: E402
+from nerf_kinematics_b200.render_core import render_chunk  # noqa: E402
+
+DEV = "cuda"
+
+
+def _ckpt(name):
+    ck = load_golden(name)
+    sdc = {k[2:]: v for k, v in ck.items() if k.startswith("c.")}
+    sdf = {k[2:]: v for k, v in ck.items() if k.startswith("f.")}
+    return sdc, sdf
+
+
+def test_cfg3_wheel_pose_path_1280x720():
+    tr = load_transforms(os.path.join(GOLD, "wheel_transforms_test_video.json"))
+    H, W, K, poses = tr["H"], tr["W"], tr["K"], tr["poses"]
+    assert (H, W) == (720, 1280) and len(poses) == 60 and abs(K[0, 0] - 674.4193) < 1e-3 and abs(K[1, 1] - 649.4572) < 1e-3
+    sdc, sdf = _ckpt("ckpt_wheel_robot6")
+    mc, mf = nk.model_from_state_dict(sdc).to(DEV), nk.model_from_state_dict(sdf).to(DEV)
+    kw = dict(network_query_fn=None, perturb=0.0, N_importance=128, network_fine=mf, N_samples=64, network_fn=mc,
+              use_viewdirs=True, white_bkgd=False, raw_noise_std=0.0, ndc=True, lindisp=False, near=0.0, far=1.0)
+    c2w = torch.from_numpy(poses[17])
+    # ---- fp32 parity on a strided subset of rows (every 120th row: 6 x 1280 rays through the CPU oracle)
+    rows = list(range(3, H, 120))
+    ro, rd = O.pixel_rays(H, W, float(K[0, 0]), c2w, K=torch.from_numpy(K))
+    rays = O.pack_rays(ro[rows], rd[rows], 0.0, 1.0, H=H, W=W, focal=float(K[0, 0]), ndc=True, use_viewdirs=True)
+    ref = O.render_rays_chunked("flexible", sdc, sdf, rays, 4096, n_coarse=64, n_fine=128, n_freq_xyz=mc.n_freq_xyz,
+                                n_freq_dir=mc.n_freq_dir)
+    with torch.no_grad():
+        rgb32, disp32, acc32, _ = nk.render(H, W, K, chunk=32768, c2w=c2w[:3, :4], precision="fp32", **kw)
+    assert rgb32.shape == (H, W, 3)
+    e_rgb = maxdiff(rgb32[rows].reshape(-1, 3), ref["rgb_fine"])
+    e_acc = maxdiff(acc32[rows].reshape(-1), ref["acc_fine"])
+    assert e_rgb <= 1e-3 and e_acc <= 1e-3, (e_rgb, e_acc)
+    # rays themselves: K-API with fx != fy, 1e-6 (north_star)
+    gro, grd = nk.get_rays(H, W, K, c2w)
+    assert maxdiff(grd[rows], rd[rows]) <= 1e-6 and torch.equal(gro[rows].cpu(), ro[rows])
+    # ---- tensor-core path, full frame: stated bound against the fp32 frame, row blocks tile it bit for bit
+    with torch.no_grad():
+        rgb16, _, acc16, _ = nk.render(H, W, K, chunk=32768, c2w=c2w[:3, :4], precision="fp16", **kw)
+        assert bool(torch.isfinite(rgb16).all()) and maxdiff(rgb16, rgb32) <= 1e-2 and maxdiff(acc16, acc32) <= 1e-2
+        parts = [parallel.render_rows(H, W, K, c2w, r, 8, chunk=32768, near=0.0, far=1.0, ndc=True, use_viewdirs=True,
+                                      precision="fp16", **{k: v for k, v in kw.items() if k not in ("ndc", "near", "far", "use_viewdirs")})[0]
+                 for r in range(8)]
+        assert torch.equal(torch.cat([p["rgb_map"] for p in parts]), rgb16)
+        # the whole 60-pose video path through the public call (2 poses here), frames in host memory
+        rgbs, disps = nk.render_path(poses[:2], (H, W, K), 32768, dict(kw, precision="fp16"))
+    assert rgbs.shape == (2, H, W, 3) and disps.shape == (2, H, W) and np.isfinite(rgbs).all()
+
+
+def _fern_scene():
+    def scene(seed):
+        sd = {k: v.clone() for k, v in O.init_tf8x256_state(seed=seed).items()}
+        sd["alpha_linear.weight"] *= 300.0
+        sd["alpha_linear.bias"] = torch.full_like(sd["alpha_linear.bias"], -3.0)
+        sd["rgb_linear.weight"] *= 8.0
+        return sd
+    return scene(0), scene(1)
+
+
+def test_cfg4_fern_504x378_ndc_viewdirs_render_and_train():
+    H, W, focal = 378, 504, 407.57
+    poses = render_path_spiral(np.eye(4, dtype=np.float32)[:3], np.array([0.0, 1.0, 0.0]), [0.3, 0.3, 0.1], 3.0, 0.2, 0.5, 2, 120)
+    assert len(poses) == 120 and poses[0].shape == (3, 4)
+    sdc, sdf = _fern_scene()
+    mc, mf = nk.model_from_state_dict(sdc).to(DEV), nk.model_from_state_dict(sdf).to(DEV)
+    kw = dict(network_query_fn=None, perturb=0.0, N_importance=128, network_fine=mf, N_samples=64, network_fn=mc,
+              use_viewdirs=True, white_bkgd=False, raw_noise_std=0.0, ndc=True, lindisp=False, near=0.0, far=1.0)
+    c2w = torch.from_numpy(np.asarray(poses[31]))
+    rows = list(range(5, H, 60))   # 7 rows x 504 rays through the oracle
+    ro, rd = O.pixel_rays(H, W, focal, torch.cat([c2w, torch.tensor([[0.0, 0, 0, 1]])]))
+    rays = O.pack_rays(ro[rows], rd[rows], 0.0, 1.0, H=H, W=W, focal=focal, ndc=True, use_viewdirs=True)
+    ref = O.render_rays_chunked("tf", sdc, sdf, rays, 4096, n_coarse=64, n_fine=128, n_freq_xyz=10, n_freq_dir=4)
+    with torch.no_grad():
+        rgb32, _, acc32, _ = nk.render(H, W, focal, chunk=32768, c2w=c2w, precision="fp32", **kw)
+        rgb16, _, acc16, _ = nk.render(H, W, focal, chunk=32768, c2w=c2w, precision="fp16", **kw)
+    assert float(ref["acc_fine"].std()) > 0.02
+    e32 = maxdiff(rgb32[rows].reshape(-1, 3), ref["rgb_fine"])
+    e16 = maxdiff(rgb16[rows].reshape(-1, 3), ref["rgb_fine"])
+    assert e32 <= 1e-3 and e16 <= 1e-2 and maxdiff(acc16[rows].reshape(-1), ref["acc_fine"]) <= 1e-2, (e32, e16)
+    assert bool(torch.isfinite(rgb16).all()) and float(acc16.max()) <= 1.0 + 1e-5
+    # ---- train step at N_rand = 4096, raw_noise_std = 1, perturb on (llff_config.txt): finite, and it learns a fixed batch
+    from nerf_kinematics_b200.trainer import TrainStep
+    st = TrainStep(mc, mf, N_samples=64, N_importance=128, perturb=1.0, raw_noise_std=1.0, white_bkgd=False, precision="fp16",
+                   lrate=5e-4, cuda_graph=True, seed=3)
+    sel = torch.from_numpy(np.random.RandomState(0).choice(H * W, 4096, replace=False)).to(DEV)
+    gro, grd = nk.get_rays(H, W, focal, c2w)
+    batch = ops.make_ray_batch(gro.reshape(-1, 3)[sel], grd.reshape(-1, 3)[sel], 0.0, 1.0, use_viewdirs=True, ndc=True, H=H, W=W,
+                               focal=focal)
+    tgt = torch.rand(4096, 3, generator=torch.Generator().manual_seed(1)).to(DEV)
+    losses = [float(st.step(batch, tgt).sum()) for _ in range(12)]
+    assert all(np.isfinite(losses)) and np.mean(losses[-3:]) < np.mean(losses[:3]), losses
+
+
+def test_cfg5_ray_batch_form_equals_chunk_calls():
+    """configs[4] hands rays in directly: the captured chunk chain (FrameRenderer external_rays, used by bench.py --mode
+    sweep) must give exactly what render_chunk gives chunk by chunk, for a ragged last chunk too."""
+    sdc, sdf = _fern_scene()
+    mc, mf = nk.model_from_state_dict(sdc).to(DEV), nk.model_from_state_dict(sdf).to(DEV)
+    g = torch.Generator().manual_seed(0)
+    n = 4096 + 777
+    o = torch.randn(n, 3, generator=g) * 0.5 + torch.tensor([0, 0, 4.0])
+    d = torch.nn.functional.normalize(torch.randn(n, 3, generator=g), dim=-1) * (0.8 + 0.4 * torch.rand(n, 1, generator=g))
+    packed = ops.make_ray_batch(o.to(DEV), d.to(DEV), 2.0, 6.0, use_viewdirs=True)
+    fr = FrameRenderer(1, n, 1.0, mc, mf, chunk=2048, near=2.0, far=6.0, ndc=False, use_viewdirs=True, N_samples=64,
+                       N_importance=128, white_bkgd=True, precision="fp16", external_rays=True)
+    with torch.no_grad():
+        a = fr.render_packed(packed, clone=True)
+        b = fr.render_packed(packed, clone=True)          # replay
+        ref = [render_chunk(packed[i:i + 2048], mc, mf, N_samples=64, N_importance=128, white_bkgd=True, precision="fp16")
+               for i in range(0, n, 2048)]
+    assert fr.replays >= 1
+    for k in ("rgb", "acc", "disp", "rgb0", "z_std"):
+        r = torch.cat([x[k] for x in ref])
+        assert torch.equal(a[k], r) and torch.equal(b[k], r), k
