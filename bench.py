@@ -535,6 +535,7 @@ def run_train(args):
             out["cpu_baseline"] = {"value": None, "unit": "rays/s", "cores": threads, "kind": "reference",
                                    "sample": "measured at N=1 only (rank 0 alone on the host)"}
         print(json.dumps(out), flush=True)
+    step.close()
     finish()
 
 

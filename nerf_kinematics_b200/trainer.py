@@ -210,11 +210,14 @@ class TrainStep:
             import torch.distributed as dist
             dist.all_reduce(self.bucket, op=dist.ReduceOp.SUM, group=self.pg)
 
-    def _fused_adam(self):
-        """nb_adam_step per network; gradients are cleared by the same pass (the next backward accumulates)."""
+    def _fused_adam(self, which=None):
+        """nb_adam_step per network (which = 0 coarse / 1 fine / None both); gradients are cleared by the same pass
+        (the next backward accumulates)."""
         with torch.cuda.device(self.dev):
             st = _stream()
-            for m, off, cnt in self._segments:
+            for i, (m, off, cnt) in enumerate(self._segments):
+                if which is not None and i != which:
+                    continue
                 check(lib().nb_adam_step(C.c_void_p(m._flat.data_ptr()), C.c_void_p(self.bucket.data_ptr() + 4 * off),
                                          C.c_void_p(self.exp_avg.data_ptr() + 4 * off),
                                          C.c_void_p(self.exp_avg_sq.data_ptr() + 4 * off), cnt,
@@ -227,6 +230,27 @@ class TrainStep:
         self.allreduce()
         self._fused_adam()
         return loss
+
+    def _device_iteration_overlapped(self, rays, target):
+        """Data-parallel iteration as ONE capturable stream program: forward + fine backward, the fine bucket's
+        all-reduce on NCCL's stream under the coarse backward, the coarse bucket's all-reduce under the fine
+        network's Adam, then the coarse network's Adam.  (NB_SPLIT_GRAPH=0; the default keeps the collectives eager
+        between three captured parts.)"""
+        import torch.distributed as dist
+        loss = self.forward_backward(rays, target, force_pack=True, zero_bucket=False, phase=1)
+        w_fine = dist.all_reduce(self.gf, op=dist.ReduceOp.SUM, group=self.pg, async_op=True)
+        self.forward_backward(rays, target, force_pack=False, zero_bucket=False, phase=2)
+        w_coarse = dist.all_reduce(self.gc, op=dist.ReduceOp.SUM, group=self.pg, async_op=True)
+        w_fine.wait()
+        self._fused_adam(which=1)
+        w_coarse.wait()
+        self._fused_adam(which=0)
+        return loss
+
+    def close(self):
+        """Drop the captured graphs (they pin NCCL resources: do this before destroy_process_group)."""
+        self._graphs.clear()
+        torch.cuda.synchronize(self.dev)
 
     def _set_hyper(self):
         """lr and bias corrections of the iteration about to run -> device (read by nb_adam_step)."""
@@ -262,9 +286,12 @@ class TrainStep:
             try:
                 graph = torch.cuda.CUDAGraph()
                 with torch.cuda.graph(graph):
-                    self._device_iteration(s_rays, s_tgt)
+                    if self.world == 1 or self.mf is None or not self._overlap:
+                        self._device_iteration(s_rays, s_tgt)
+                    else:
+                        self._device_iteration_overlapped(s_rays, s_tgt)
                 g = (graph, None, s_rays, s_tgt, None)
-            except Exception:  # collective not capturable on this stack: capture the two local halves instead
+            except Exception:  # collective not capturable on this stack: capture the local parts instead
                 if self.world == 1:
                     raise
                 self._split_graph = True
