@@ -64,6 +64,12 @@ int nb_device_count(void);
 int64_t nb_launch_count(void);
 void nb_launch_count_reset(void);
 
+/* Process-wide kernel selection knobs (no effect on results beyond rounding order).  Returns the previous value (>= 0) or
+ * NB_ERR_INVALID for an unknown name.
+ *   "fwd_2cta": 1 = inference launches of the tensor-core MLP use the CTA-pair kernel (tcgen05 cta_group::2: two SMs share
+ *               every weight slot), 0 = the single-CTA kernel.  Initial value: environment NB_FWD_2CTA, else 0. */
+int nb_set_option(const char* name, int value);
+
 /* ---------------------------------------------------------------- model handle
  * Replaces: TF create_nerf/init_nerf_model (nerf/run_nerf.py:378-404, run_nerf_helpers.py:80-118) and
  * PT FlexibleNeRFModel.__init__ (models.py:186-231) as far as the *weights layout* is concerned.

@@ -45,6 +45,7 @@ SIGNATURES = {
     "nb_abi_version": (i32, []),
     "nb_last_error": (C.c_char_p, []),
     "nb_device_count": (i32, []),
+    "nb_set_option": (i32, [C.c_char_p, i32]),
     "nb_launch_count": (i64, []),
     "nb_launch_count_reset": (None, []),
     "nb_model_create": (i32, [i32, i32, i32, i32, i32, i32, i32, C.POINTER(p)]),

@@ -517,6 +517,338 @@ mlp_tc_kernel(const __grid_constant__ TcPlan plan, const unsigned char* __restri
   }
 }
 
+// ------------------------------------------------------------------------------------ CTA-pair forward kernel
+// Same network, same roles, same step program as mlp_tc_kernel, for inference (no activation record), run by CLUSTERS OF
+// TWO CTAs (two SMs of a TPC).  Each CTA still owns two 128-point tiles; MMA stream t joins tile t of both CTAs into
+// one tcgen05.mma.cta_group::2 of M = 256: the leader CTA (cluster rank 0) issues it, every CTA supplies its own 128
+// activation rows and HALF of the weight rows (N/2) from its own shared memory.  Per SM the B-operand reads and the
+// weight ring fill are half of the single-CTA kernel's -- the shared-memory port is what that kernel saturates
+//  -- and the ring holds twice as many slots.
+//   * barriers the issuers wait on live in the leader; the peer CTA's epilogue warps arrive on them remotely
+//     (mbarrier.arrive.release.cluster on the mapa address), one arrival per warp;
+//   * a weight slot is ready when BOTH halves have landed: the peer's warp 1 relays its local "full" barrier to the
+//     leader's peer_full barrier;
+//   * tcgen05.commit multicasts its arrival to both CTAs (slot free, accumulator ready).
+constexpr int kRing2 = 6;
+constexpr int kSlot2Bytes = 128 * 64;   // half of a <= 256-row slot
+
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreadsTc, 1)
+mlp_tc2_kernel(const __grid_constant__ TcPlan plan, const unsigned char* __restrict__ wpk, const float* __restrict__ bias_g,
+               TcSrc src, long long n_points, float* __restrict__ raw) {
+  extern __shared__ __align__(1024) unsigned char smem_raw[];
+  unsigned char* smem = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  const int tile_blocks = plan.n_act_blocks + 1;
+  const int tile_bytes = tile_blocks * kBlockBytes;
+  unsigned char* act = smem;                                 // [2 tiles][tile_blocks][16 KB]
+  unsigned char* ring = act + 2 * tile_bytes;                // [kRing2][8 KB]
+  float* bias_s = reinterpret_cast<float*>(ring + kRing2 * kSlot2Bytes);
+  float* alpha_part = bias_s + ((plan.n_bias + 3) & ~3);     // [2 tiles][2 parities][128 rows]
+  uint64_t* bars = reinterpret_cast<uint64_t*>(alpha_part + 2 * 2 * kTileM);
+  uint64_t* bar_full = bars;                    // [kRing2] this CTA's half of the slot has landed
+  uint64_t* bar_pfull = bar_full + kRing2;      // [kRing2] (leader) the peer's half has landed
+  uint64_t* bar_empty = bar_pfull + kRing2;     // [kRing2] both MMA streams have consumed the slot (multicast commits)
+  uint64_t* bar_enc = bar_empty + kRing2;       // [2]  (leader) position encoding of stream t written in both CTAs (16 warps)
+  uint64_t* bar_encd = bar_enc + 2;             // [2]  (leader) direction encoding (8 warps)
+  uint64_t* bar_act = bar_encd + 2;             // [2][4] (leader) activation block j of stream t written (8 warps)
+  uint64_t* bar_drain = bar_act + 8;            // [2]  (leader) accumulator of stream t read out (16 warps)
+  uint64_t* bar_acc = bar_drain + 2;            // [2]  accumulator of stream t complete (multicast commit)
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bar_acc + 2);
+  uint4* prog = reinterpret_cast<uint4*>(tmem_slot + 4);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const uint32_t rank = cluster_ctarank();
+  const bool leader = rank == 0;
+  const long long n_tiles = (n_points + kTileM - 1) / kTileM;
+  const long long n_clusters = gridDim.x >> 1, cluster = blockIdx.x >> 1;
+  // contiguous, balanced tile range of this cluster, taken four tiles at a time:
+  // round tiles base + {0, 1, 2, 3} = (stream 0, CTA 0), (stream 0, CTA 1), (stream 1, CTA 0), (stream 1, CTA 1)
+  const long long tile_begin = n_tiles * cluster / n_clusters;
+  const long long tile_end = n_tiles * (cluster + 1) / n_clusters;
+
+  if (threadIdx.x == 0) {
+    for (int i = 0; i < kRing2; ++i) {
+      mbar_init(smem_u32(bar_full + i), 1);
+      mbar_init(smem_u32(bar_pfull + i), 1);
+      mbar_init(smem_u32(bar_empty + i), 2);
+    }
+    for (int t = 0; t < 2; ++t) {
+      mbar_init(smem_u32(bar_acc + t), 1);
+      mbar_init(smem_u32(bar_enc + t), 16);
+      mbar_init(smem_u32(bar_encd + t), 8);
+      for (int i = 0; i < 4; ++i) mbar_init(smem_u32(bar_act + 4 * t + i), 8);
+      mbar_init(smem_u32(bar_drain + t), 16);
+    }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (threadIdx.x == 96) {
+    int i = 0;
+    bool encd_pending = false;
+    for (int s = 0; s < plan.n_stages; ++s) {
+      const TcStage& st = plan.st[s];
+      for (int kb = 0; kb < st.n_kb; ++kb) {
+        const int sidx = st.a_src[kb];
+        for (int h = sidx == SRC_BIAS ? 1 : 0; h < 2; ++h) {
+          uint4 e;
+          e.x = (uint32_t)((sidx < 4 ? sidx : plan.n_act_blocks) * kBlockBytes + h * 64);
+          e.y = umma_idesc2(st.n_main);
+          e.z = sidx == SRC_BIAS ? PF_BIAS : 0u;
+          e.w = 0u;
+          if (h == 0 && sidx < 4) e.z |= PF_WAIT_ACT | (uint32_t)sidx;
+          if ((sidx == SRC_ENCD || sidx == SRC_BIAS) && encd_pending) { e.z |= PF_WAIT_ENCD; encd_pending = false; }
+          if (kb == 0 && h == 0) e.z |= PF_FIRST;
+          if (kb == st.n_kb - 1 && h == 1) e.z |= PF_LAST;
+          if ((kb | h) != 0) e.z |= PF_ACC;
+          prog[i++] = e;
+        }
+      }
+      if (st.write_encd) encd_pending = true;
+    }
+  }
+  if (warp == 1) {  // TMEM: all 512 columns in both CTAs of the pair; stream t owns columns [256 t, 256 t + 256)
+    asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "r"(512));
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;");
+  }
+  for (int i = threadIdx.x; i < plan.n_bias; i += blockDim.x) bias_s[i] = bias_g[i];
+  tc_fence_before();
+  __syncthreads();
+  cluster_sync_all();   // barriers of both CTAs are initialised before anybody arrives on a remote one
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+  const int n_steps = plan.n_steps;
+  // rounds of this cluster and which streams are populated in the last one
+  const long long n_local = tile_end - tile_begin;
+  const long long n_rounds = (n_local + 3) >> 2;
+
+  if (warp == 0) {
+    // ============================ weight producer: this CTA's half of every slot ============================
+    if (lane == 0) {
+      uint32_t slot = 0, phase = 0;
+      const uint64_t pol_w = l2_evict_last();
+      for (long long rd = 0; rd < n_rounds; ++rd) {
+        for (int s = 0; s < plan.n_stages; ++s) {
+          const TcStage& st = plan.st[s];
+          const uint32_t half_rows_bytes = (uint32_t)(st.n_main >> 1) * 64u;   // N/2 rows x 32 K-elements
+          for (int kb = 0; kb < st.n_kb; ++kb) {
+            for (int h = st.a_src[kb] == SRC_BIAS ? 1 : 0; h < 2; ++h) {
+              mbar_wait(smem_u32(bar_empty + slot), phase ^ 1);
+              const uint32_t fb = smem_u32(bar_full + slot);
+              mbar_expect_tx(fb, half_rows_bytes);
+              bulk_g2s_hint(smem_u32(ring + slot * kSlot2Bytes),
+                            wpk + st.w_off + (size_t)kb * st.chunk_bytes + (size_t)h * (st.n_main * 64u) + (size_t)rank * half_rows_bytes,
+                            half_rows_bytes, fb, pol_w);
+              if (++slot == kRing2) { slot = 0; phase ^= 1; }
+            }
+          }
+        }
+      }
+    }
+  } else if (warp == 1 && !leader) {
+    // ============================ peer: relay "my half has landed" to the leader ============================
+    if (lane == 0) {
+      uint32_t slot = 0, phase = 0;
+      const uint32_t pf0 = mapa_u32(smem_u32(bar_pfull), 0);
+      for (long long it = 0; it < n_rounds * n_steps; ++it) {
+        mbar_wait(smem_u32(bar_full + slot), phase);
+        mbar_arrive_cluster(pf0 + 8 * slot);
+        if (++slot == kRing2) { slot = 0; phase ^= 1; }
+      }
+    }
+  } else if ((warp == 1 || warp == 2) && leader) {
+    // ============================ MMA issuers of the pair (one warp per stream) ============================
+    const int t = warp - 1;
+    uint32_t slot = 0, phase = 0;
+    uint32_t ph_act = 0, ph_enc = 0, ph_encd = 0, ph_drain = 0;
+    bool armed = false;
+    const uint32_t act_s = smem_u32(act) + t * tile_bytes, ring_s = smem_u32(ring);
+    const uint32_t bar_full_s = smem_u32(bar_full), bar_pfull_s = smem_u32(bar_pfull), bar_empty_s = smem_u32(bar_empty);
+    const uint32_t bar_act_s = smem_u32(bar_act + 4 * t);
+    const uint32_t bar_enc_s = smem_u32(bar_enc + t), bar_encd_s = smem_u32(bar_encd + t);
+    const uint32_t bar_drain_s = smem_u32(bar_drain + t), bar_acc_s = smem_u32(bar_acc + t);
+    const uint32_t d_tmem = tmem_base + t * 256;
+    for (long long rd = 0; rd < n_rounds; ++rd) {
+      const bool active = tile_begin + 4 * rd + 2 * t < tile_end;   // the stream has at least its CTA-0 tile
+      if (!active) {
+        // unpopulated stream of the last round: only keep the ring's two-commit protocol going
+        for (int i = 0; i < n_steps; ++i) {
+          mbar_wait(bar_full_s + 8 * slot, phase);
+          mbar_wait_cluster(bar_pfull_s + 8 * slot, phase);
+          if (elect_one()) tc_commit2(bar_empty_s + 8 * slot);
+          __syncwarp();
+          if (++slot == kRing2) { slot = 0; phase ^= 1; }
+        }
+        continue;
+      }
+      mbar_wait_cluster(bar_enc_s, ph_enc);
+      ph_enc ^= 1;
+      uint4 e = prog[0];
+      for (int i = 0; i < n_steps; ++i) {
+        const uint4 en = prog[i + 1 < n_steps ? i + 1 : i];
+        const uint32_t fl = e.z;
+        if (fl & PF_WAIT_ACT) {
+          const uint32_t j = fl & 3u;
+          mbar_wait_cluster(bar_act_s + 8 * j, (ph_act >> j) & 1u);
+          ph_act ^= 1u << j;
+        } else if (fl & PF_WAIT_ENCD) {
+          mbar_wait_cluster(bar_encd_s, ph_encd);
+          ph_encd ^= 1;
+        }
+        if ((fl & PF_FIRST) && armed) {
+          mbar_wait_cluster(bar_drain_s, ph_drain);
+          ph_drain ^= 1;
+        }
+        armed = true;
+        mbar_wait(bar_full_s + 8 * slot, phase);
+        mbar_wait_cluster(bar_pfull_s + 8 * slot, phase);
+        tc_fence_after();
+        const uint64_t a_desc = kDescHiSw128 | (uint64_t)(((act_s + e.x) & 0x3FFFFu) >> 4);
+        const uint64_t b_desc = kDescHiSw64 | (uint64_t)(((ring_s + slot * kSlot2Bytes) & 0x3FFFFu) >> 4);
+        if (elect_one()) {
+          if (!(fl & PF_BIAS)) tc_mma2(d_tmem, a_desc, b_desc, e.y, (fl & PF_ACC) ? 1u : 0u);
+          tc_mma2(d_tmem, a_desc + 2, b_desc + 2, e.y, 1u);
+          tc_commit2(bar_empty_s + 8 * slot);
+          if (fl & PF_LAST) tc_commit2(bar_acc_s);
+        }
+        __syncwarp();
+        if (++slot == kRing2) { slot = 0; phase ^= 1; }
+        e = en;
+      }
+    }
+  } else if (warp >= 4) {
+    // ============================ epilogue warps (thread == row), both CTAs ============================
+    const int ew = warp - 4;
+    const int t = ew >> 3;
+    const int par = (ew >> 2) & 1;
+    const int q = warp & 3;
+    const int row = q * 32 + lane;
+    const int sw = row & 7;
+    const uint32_t t_main = tmem_base + (((uint32_t)(q * 32)) << 16) + t * 256;
+    unsigned char* act_t = act + t * tile_bytes;
+    unsigned char* enc_t = act_t + plan.n_act_blocks * kBlockBytes;
+    float* apart = alpha_part + (t * 2 + par) * kTileM;
+    // the issuers' barriers live in the leader CTA
+    const uint32_t l_enc = mapa_u32(smem_u32(bar_enc + t), 0), l_encd = mapa_u32(smem_u32(bar_encd + t), 0);
+    const uint32_t l_act = mapa_u32(smem_u32(bar_act + 4 * t), 0), l_drain = mapa_u32(smem_u32(bar_drain + t), 0);
+    uint32_t acc_phase = 0;
+    for (long long rd = 0; rd < n_rounds; ++rd) {
+      const long long stream_tile0 = tile_begin + 4 * rd + 2 * t;
+      if (stream_tile0 >= tile_end) break;          // this stream is not populated in the cluster's last round
+      const long long tile = stream_tile0 + rank;   // may be one past the range: a dummy tile (clamped points, no store)
+      const bool tile_real = tile < tile_end;
+      long long p = tile * kTileM + row;
+      const bool in_range = tile_real && p < n_points;
+      if (p >= n_points) p = n_points - 1;
+      float v0 = 0.f, v1 = 0.f, v2 = 0.f;
+      {
+        float x0, x1, x2;
+        if (src.rays != nullptr) {
+          const long long r = p / src.S;
+          const float* ry = src.rays + r * src.stride;
+          const float zz = src.z[p];
+          x0 = __fadd_rn(ry[0], __fmul_rn(ry[3], zz));
+          x1 = __fadd_rn(ry[1], __fmul_rn(ry[4], zz));
+          x2 = __fadd_rn(ry[2], __fmul_rn(ry[5], zz));
+          if (plan.Cd > 0 && par == 1) { v0 = ry[8]; v1 = ry[9]; v2 = ry[10]; }
+        } else {
+          x0 = src.pts[3 * p]; x1 = src.pts[3 * p + 1]; x2 = src.pts[3 * p + 2];
+          if (plan.Cd > 0 && par == 1) {
+            const float* vv = src.viewdirs + (p / src.per_dir) * 3;
+            v0 = vv[0]; v1 = vv[1]; v2 = vv[2];
+          }
+        }
+        if (par == 0) encode_row<0, 4>(enc_t, row, x0, x1, x2, plan.Lx);
+        else encode_row<4, 4>(enc_t, row, x0, x1, x2, plan.Lx);
+      }
+      fence_async_smem();
+      __syncwarp();
+      if (lane == 0) mbar_arrive_cluster(l_enc);
+
+      for (int s = 0; s < plan.n_stages; ++s) {
+        const TcStage& st = plan.st[s];
+        mbar_wait(smem_u32(bar_acc + t), acc_phase);
+        acc_phase ^= 1;
+        tc_fence_after();
+        const float* bs = bias_s + st.b_off;
+        if (st.epi == EPI_HIDDEN) {
+          const bool relu = st.relu != 0;
+          const int nblk = st.n_act >> 6;
+          float adot = 0.0f;
+          if (par >= nblk) {
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive_cluster(l_drain);
+          }
+          for (int j = par; j < nblk; j += 2) {
+            uint32_t v[64];
+            NB_TMEM_LD32(t_main + j * 64, v);
+            {
+              uint32_t* v2p = v + 32;
+              NB_TMEM_LD32(t_main + j * 64 + 32, v2p);
+            }
+            tc_wait_ld();
+            if (j + 2 >= nblk) {
+              tc_fence_before();
+              __syncwarp();
+              if (lane == 0) mbar_arrive_cluster(l_drain);
+            }
+            const uint32_t rp = smem_u32(act_t) + j * kBlockBytes + row * 128;
+            if (st.alpha_dot) {
+              const uint32_t wa = smem_u32(bias_s) + (plan.alpha_w_off + j * 64) * 4;
+              epi_convert32<true>(v, 0, rp, wa, sw, relu, adot);
+              epi_convert32<true>(v, 32, rp, wa, sw, relu, adot);
+            } else if (relu) {
+              epi_convert32<false, 1>(v, 0, rp, 0u, sw, true, adot);
+              epi_convert32<false, 1>(v, 32, rp, 0u, sw, true, adot);
+            } else {
+              epi_convert32<false, 0>(v, 0, rp, 0u, sw, false, adot);
+              epi_convert32<false, 0>(v, 32, rp, 0u, sw, false, adot);
+            }
+            fence_async_smem();
+            __syncwarp();
+            if (lane == 0) mbar_arrive_cluster(l_act + 8 * j);
+          }
+          if (st.alpha_dot) apart[row] = adot;
+          if (st.write_encd && par == 1) {
+            encode_row<0, 8>(enc_t, row, v0, v1, v2, plan.Ld);
+            fence_async_smem();
+            __syncwarp();
+            if (lane == 0) mbar_arrive_cluster(l_encd);
+          }
+        } else {
+          uint32_t v[4] = {0u, 0u, 0u, 0u};
+          if (par == 0) {
+            tmem_ld4(t_main, v);
+            tc_wait_ld();
+          }
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive_cluster(l_drain);
+          if (par == 0) {
+            float4 o;
+            o.x = __uint_as_float(v[0]) + bs[0];
+            o.y = __uint_as_float(v[1]) + bs[1];
+            o.z = __uint_as_float(v[2]) + bs[2];
+            if (st.epi == EPI_RGB) {
+              const float* ap = alpha_part + (t * 2) * kTileM;
+              o.w = ap[row] + ap[kTileM + row] + bias_s[plan.alpha_b_off];
+            } else {
+              o.w = __uint_as_float(v[3]) + bs[3];
+            }
+            if (in_range) reinterpret_cast<float4*>(raw)[tile * kTileM + row] = o;
+          }
+        }
+      }
+    }
+  }
+  // ---- teardown: nobody leaves (or frees tensor memory) while the other CTA may still signal or be signalled
+  tc_fence_before();
+  __syncthreads();
+  cluster_sync_all();
+  if (warp == 1) {
+    __syncwarp();
+    asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(512));
+  }
+}
+
 // ------------------------------------------------------------------------------------ host: plan + packing
 void packed_free(PackedBf16* p) {
   if (p == nullptr) return;
@@ -645,6 +977,29 @@ static size_t tc_smem_bytes(const TcPlan& plan) {
   return b;
 }
 
+static size_t tc2_smem_bytes(const TcPlan& plan) {
+  size_t b = 1024;  // alignment slack
+  b += (size_t)2 * (plan.n_act_blocks + 1) * kBlockBytes;
+  b += (size_t)kRing2 * kSlot2Bytes;
+  b += (size_t)((plan.n_bias + 3) & ~3) * sizeof(float);
+  b += (size_t)2 * 2 * kTileM * sizeof(float);
+  b += (3 * kRing2 + 2 + 2 + 8 + 2 + 2) * sizeof(uint64_t) + 16;
+  b += (size_t)plan.n_steps * sizeof(uint4);
+  return b;
+}
+
+// NB_FWD_2CTA: 1 = inference launches use the CTA-pair kernel (mlp_tc2_kernel), 0 = the single-CTA kernel
+static int g_fwd_2cta = -1;
+static int fwd_2cta_mode() {
+  if (g_fwd_2cta < 0) g_fwd_2cta = getenv("NB_FWD_2CTA") ? atoi(getenv("NB_FWD_2CTA")) : 0;
+  return g_fwd_2cta;
+}
+int set_fwd_2cta(int v) {
+  const int old = fwd_2cta_mode();
+  g_fwd_2cta = v != 0;
+  return old;
+}
+
 int packed_build(nb_model* m, cudaStream_t stream) {
   if (m->packed == nullptr) {
     PackedBf16* p = new PackedBf16();
@@ -677,6 +1032,8 @@ int packed_build(nb_model* m, cudaStream_t stream) {
     if (e == cudaSuccess) e = cudaStreamSynchronize(stream);  // the host vectors die with this scope
     if (e == cudaSuccess)
       e = cudaFuncSetAttribute(mlp_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+    if (e == cudaSuccess)
+      e = cudaFuncSetAttribute(mlp_tc2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
     if (e != cudaSuccess) {
       packed_free(p);
       set_error("bf16 pack setup failed: %s", cudaGetErrorString(e));
@@ -726,6 +1083,14 @@ int tc_forward(const nb_model* m, const float* rays, int ray_stride, const float
   }
   TcSrc src{rays, ray_stride, z_vals, n_samples > 0 ? n_samples : 1, pts, viewdirs, points_per_dir > 0 ? points_per_dir : 1};
   const int64_t n_tiles = ceil_div(n_points, kTileM);
+  if (rec == nullptr && fwd_2cta_mode() != 0 && tc2_smem_bytes(p->plan) <= 227 * 1024) {
+    // CTA-pair kernel: clusters of 2 CTAs, four tiles per cluster round
+    const int clusters = (int)std::min<int64_t>(ceil_div(n_tiles, 4), sm_count() / 2);
+    mlp_tc2_kernel<<<2 * clusters, kThreadsTc, tc2_smem_bytes(p->plan), stream>>>(p->plan, p->d_w, p->d_bias, src,
+                                                                                 (long long)n_points, raw);
+    NB_LAUNCHED();
+    return NB_OK;
+  }
   const int grid = (int)std::min<int64_t>(ceil_div(n_tiles, 2), sm_count());
   // Timing experiments behind the numbers in DESIGN.md (results are then garbage) exist only in builds made with
   // -DNB_TIMING_EXPERIMENTS: NB_FWD_DEBUG=1 producer skips the weight loads, 2 = epilogue skips the conversion
@@ -740,3 +1105,11 @@ int tc_forward(const nb_model* m, const float* rays, int ray_stride, const float
 }
 
 }  // namespace nb
+
+extern "C" int nb_set_option(const char* name, int value) {
+  using namespace nb;
+  NB_REQUIRE(name != nullptr, "nb_set_option: null name");
+  if (strcmp(name, "fwd_2cta") == 0) return set_fwd_2cta(value);
+  set_error("nb_set_option: unknown option '%s'", name);
+  return NB_ERR_INVALID;
+}
