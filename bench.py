@@ -301,7 +301,8 @@ def measure_render(H, W, K, poses, kw, chunk, steps, warmup, rank, world, barrie
     dev = next(kw["network_fn"].parameters()).device
     r0, r1 = parallel.row_block(H, rank, world)
     rk = {k: v for k, v in kw.items() if k not in ("ndc", "near", "far", "use_viewdirs")}
-    fr = _frame_renderer(H, W, K, chunk, kw["ndc"], kw["near"], kw["far"], kw["use_viewdirs"], rk, rows=(r0, r1))
+    with torch.no_grad():
+        fr = _frame_renderer(H, W, K, chunk, kw["ndc"], kw["near"], kw["far"], kw["use_viewdirs"], rk, rows=(r0, r1))
     assert fr is not None
     M = len(poses)
     poses_dev = [torch.as_tensor(np.asarray(p, dtype=np.float32)[:3, :4]).to(dev) for p in poses]
@@ -487,7 +488,7 @@ def run_train(args):
             render_obj = render_summary(m, frames, world, peaks()["bf16_tflops"])
             render_obj["workload"] = WORKLOADS["render"]
         except Exception as ex:  # reported, never fatal for the headline
-            render_obj = {"failed": str(ex)}
+            render_obj = {"failed": "%s: %s" % (type(ex).__name__, ex)}
     if rank == 0:
         pk = peaks()
         peak = pk["bf16_tflops"]

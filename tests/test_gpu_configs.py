@@ -75,8 +75,8 @@ def test_cfg3_wheel_pose_path_1280x720():
 def _fern_scene():
     def scene(seed):
         sd = {k: v.clone() for k, v in O.init_tf8x256_state(seed=seed).items()}
-        sd["alpha_linear.weight"] *= 300.0
-        sd["alpha_linear.bias"] = torch.full_like(sd["alpha_linear.bias"], -3.0)
+        sd["alpha_linear.weight"] *= 30.0
+        sd["alpha_linear.bias"] = torch.full_like(sd["alpha_linear.bias"], -0.2)
         sd["rgb_linear.weight"] *= 8.0
         return sd
     return scene(0), scene(1)

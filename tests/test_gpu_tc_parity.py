@@ -2,9 +2,9 @@
 end to end at >= 10 000 rays: the north_star bound (<= 1e-2 max-abs on rgb / acc, <= 0.05 dB PSNR) for the plain,
 the NDC + viewdirs (fern shape scaled down) and the lindisp configurations, plus what happens beyond the fp16 range.
 
-The scene is a seeded random-init 8x256 pair whose density head is sharpened (alpha weights x300, bias -3) so that
-acc spreads over [0.3, 1] instead of the near-empty volume a default init renders: the importance sampling and the
-compositing then see realistic, peaky weights and every error of the network is amplified 300x into sigma."""
+The scene is a seeded random-init 8x256 pair whose density head is sharpened (alpha weights x30, bias -0.2) so that
+acc spreads over [0.1, 1] instead of the near-empty volume a default init renders: the importance sampling and the
+compositing then see realistic, peaky weights and every error of the network is amplified 30x into sigma."""
 import numpy as np
 import pytest
 import torch
@@ -22,8 +22,8 @@ DEV = "cuda"
 
 def _scene(seed, lx=10):
     sd = {k: v.clone() for k, v in O.init_tf8x256_state(seed=seed, input_ch=3 + 6 * lx).items()}
-    sd["alpha_linear.weight"] *= 300.0
-    sd["alpha_linear.bias"] = torch.full_like(sd["alpha_linear.bias"], -3.0)
+    sd["alpha_linear.weight"] *= 30.0
+    sd["alpha_linear.bias"] = torch.full_like(sd["alpha_linear.bias"], -0.2)
     sd["rgb_linear.weight"] *= 8.0
     return sd
 
