@@ -342,6 +342,7 @@ def measure_render(H, W, K, poses, kw, chunk, steps, warmup, rank, world, barrie
 
 
 def render_summary(m, steps, world, peak):
+    sustained = peaks().get("bf16_tflops_sustained")
     rate = m["rays_per_frame"] * steps / m["t_res"]
     e2e = m["rays_per_frame"] * steps / m["t_e2e"]
     return {"value": rate, "unit": "rays/s", "ms_per_frame": 1e3 * m["t_res"] / steps,
@@ -349,7 +350,9 @@ def render_summary(m, steps, world, peak):
                     "d2h_bytes_per_step": m["rays_per_frame"] * 16, "ms_per_step": 1e3 * m["t_e2e"] / steps},
             "roofline": {"bound": "tensor", "kernel": "whole frame (all kernels of render())",
                          "achieved": rate / world * FLOPS_PER_RAY_RENDER / 1e12, "peak": peak, "unit": "TFLOP/s",
-                         "frac": rate / world * FLOPS_PER_RAY_RENDER / 1e12 / peak},
+                         "frac": rate / world * FLOPS_PER_RAY_RENDER / 1e12 / peak,
+                         "peak_sustained": sustained,   # a frame is a long step: the power-capped clock applies
+                         "frac_of_sustained": (rate / world * FLOPS_PER_RAY_RENDER / 1e12 / sustained) if sustained else None},
             "frames": steps, "gpu_launches": m["launches"], "finite": m["finite"]}
 
 

@@ -176,6 +176,9 @@ int nb_mlp_backward(const nb_model_t* m, int precision, int64_t n_points, float*
  * `workspace`, of the per-tile X record (forward operand tiles: [encx, encd, activations of every stage]) and dZ record
  * (gradient tiles in dgrad-chain order), and their sizes in 16 KB blocks (128 points x 64 fp16, SWIZZLE_128B image)
  * per 128-point tile.  Used by the parity tests to check dgrad / wgrad exactly against the saved activations. */
+/* The constant the NB_PREC_F16 path scales its hidden activations by (a power of two; see csrc/tc_common.cuh kActScale):
+ * activation blocks of the X record hold scale * h, the encoding blocks (0, 1) true values. */
+float nb_mlp_activation_scale(void);
 int nb_mlp_record_layout(const nb_model_t* m, int64_t n_points, const void* workspace, int64_t* xrec_offset,
                          int* xrec_blocks, int64_t* drec_offset, int* drec_blocks);
 

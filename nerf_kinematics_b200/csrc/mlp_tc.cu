@@ -53,7 +53,7 @@ __device__ __forceinline__ void pack_weights_body(const float* __restrict__ para
   for (int e = 0; e < 8; ++e) {
     const int k = c * 8 + e;
     // element 63 multiplies the encoding block's constant-one channel: the layer's bias rides along in the MMA
-    v[e] = k < sg.ncols ? src[k] : (k == 63 && sg.bias_off >= 0 ? params[sg.bias_off + r] : 0.0f);
+    v[e] = (k < sg.ncols ? src[k] : (k == 63 && sg.bias_off >= 0 ? params[sg.bias_off + r] : 0.0f)) * sg.scale;
   }
   uint4 pk;
   pk.x = pack_h2(v[0], v[1], false);
@@ -492,15 +492,16 @@ mlp_tc_kernel(const __grid_constant__ TcPlan plan, const unsigned char* __restri
           mbar_arrive(smem_u32(bar_drain + t));
           if (par == 0) {
             float4 o;
-            o.x = __uint_as_float(v[0]) + bs[0];
-            o.y = __uint_as_float(v[1]) + bs[1];
-            o.z = __uint_as_float(v[2]) + bs[2];
+            // the heads read kActScale * h: undo the scale in fp32, then add the (unscaled, fp32) bias
+            o.x = __uint_as_float(v[0]) * kInvActScale + bs[0];
+            o.y = __uint_as_float(v[1]) * kInvActScale + bs[1];
+            o.z = __uint_as_float(v[2]) * kInvActScale + bs[2];
             if (st.epi == EPI_RGB) {
               const float* ap = alpha_part + (t * 2) * kTileM;
-              alpha_raw = ap[row] + ap[kTileM + row] + bias_s[plan.alpha_b_off];
+              alpha_raw = (ap[row] + ap[kTileM + row]) * kInvActScale + bias_s[plan.alpha_b_off];
               o.w = alpha_raw;
             } else {
-              o.w = __uint_as_float(v[3]) + bs[3];
+              o.w = __uint_as_float(v[3]) * kInvActScale + bs[3];
             }
             if (in_range) reinterpret_cast<float4*>(raw)[tile * kTileM + row] = o;
           }
@@ -824,14 +825,14 @@ mlp_tc2_kernel(const __grid_constant__ TcPlan plan, const unsigned char* __restr
           if (lane == 0) mbar_arrive_cluster(l_drain);
           if (par == 0) {
             float4 o;
-            o.x = __uint_as_float(v[0]) + bs[0];
-            o.y = __uint_as_float(v[1]) + bs[1];
-            o.z = __uint_as_float(v[2]) + bs[2];
+            o.x = __uint_as_float(v[0]) * kInvActScale + bs[0];
+            o.y = __uint_as_float(v[1]) * kInvActScale + bs[1];
+            o.z = __uint_as_float(v[2]) * kInvActScale + bs[2];
             if (st.epi == EPI_RGB) {
               const float* ap = alpha_part + (t * 2) * kTileM;
-              o.w = ap[row] + ap[kTileM + row] + bias_s[plan.alpha_b_off];
+              o.w = (ap[row] + ap[kTileM + row]) * kInvActScale + bias_s[plan.alpha_b_off];
             } else {
-              o.w = __uint_as_float(v[3]) + bs[3];
+              o.w = __uint_as_float(v[3]) * kInvActScale + bs[3];
             }
             if (in_range) reinterpret_cast<float4*>(raw)[tile * kTileM + row] = o;
           }
@@ -890,6 +891,7 @@ static bool build_plan(const Graph& g, TcPlan& plan, std::vector<PackSeg>& segs,
   auto add_kb = [&](TcStage& st, int a_src, PackSeg sg) {
     sg.dst_off = (long long)woff;
     sg.chunk_rows = st.n_main;
+    sg.scale = (a_src == SRC_ENCX || a_src == SRC_ENCD || a_src == SRC_BIAS) ? kActScale : 1.0f;
     segs.push_back(sg);
     st.a_src[st.n_kb++] = a_src;
     woff += st.chunk_bytes;
@@ -1105,6 +1107,8 @@ int tc_forward(const nb_model* m, const float* rays, int ray_stride, const float
 }
 
 }  // namespace nb
+
+extern "C" float nb_mlp_activation_scale(void) { return nb::kActScale; }
 
 extern "C" int nb_set_option(const char* name, int value) {
   using namespace nb;

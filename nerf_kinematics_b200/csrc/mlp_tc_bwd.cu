@@ -534,7 +534,9 @@ __global__ void wgrad_reduce_kernel(const __grid_constant__ WgPlan plan, const _
     if (wr < 0 || wr >= u.out_rows || cc >= u.x_valid[xs]) return;
     float s = 0.0f;
     for (int p = p0; p < p1; ++p) s += a.part_w[(size_t)p * kPartFloats + e];
-    grad[u.w_off + (long long)wr * u.ld + u.x_col0[xs] + cc] += s * inv;
+    // X-record blocks 0 / 1 are the encodings (true values); every other block holds kActScale * activation
+    const float xinv = u.x_blk[xs] >= 2 ? kInvActScale : 1.0f;
+    grad[u.w_off + (long long)wr * u.ld + u.x_col0[xs] + cc] += s * inv * xinv;
   } else if (e < M * Ntot + 256) {
     const int j = e - M * Ntot, wr = j - u.row0;
     if (u.b_off < 0 || wr < 0 || wr >= u.out_rows) return;

@@ -17,6 +17,16 @@
 
 namespace nb {
 
+// Activation scale of the 16-bit path.  Hidden activations are carried as fp16 (11 significand bits, range 65 504);
+// shipped checkpoints reach ~1.1e5 in their trunk (wheel_robot6 at 1280x720) and would clamp.  ReLU networks are
+// positively homogeneous, so the packed image multiplies every weight that reads an ENCODING block, and every bias, by
+// kActScale = 2^-5: all hidden activations become kActScale * h (exact: a power of two; range 2.1e6, values below
+// 2e-3 lose relative -- not absolute, <= 2e-6 -- precision), hidden-to-hidden weights are untouched, and the heads'
+// fp32 epilogue multiplies by kInvActScale.  The backward sees scaled X records: the wgrad reduce divides the
+// sub-matrices whose X operand is an activation block by kActScale (dz and the bias gradients are unaffected).
+constexpr float kActScale = 0.03125f;
+constexpr float kInvActScale = 32.0f;
+
 constexpr int kMaxStages = 14;
 constexpr int kMaxKB = 6;
 constexpr int kRing = 3;
@@ -106,6 +116,7 @@ struct PackSeg {
   int row0, n_rows;   // chunk rows [row0, row0+n_rows) <- source rows [0, n_rows)
   int chunk_rows;     // rows of the whole chunk (the stage's N)
   int ld, col0, ncols;  // source leading dim; chunk element k <- source column col0+k for k < ncols, else 0
+  float scale;          // kActScale for chunks that multiply an encoding block (and the bias riding in them), else 1
 };
 // transposed chunk for the dgrad chain: chunk row n (layer input), element kdst0+k <- W[krow0+k, col0+n], k < kcount
 struct PackSegT {
@@ -273,15 +284,19 @@ __device__ __forceinline__ uint32_t mapa_u32(uint32_t saddr, uint32_t rank) {
   return r;
 }
 __device__ __forceinline__ void mbar_arrive_cluster(uint32_t cluster_addr) {
-  asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
+  // default (CTA-scope release) semantics on purpose: the .release.cluster form costs a MEMBAR.ALL.GPU per arrival.  What
+  // the arrival publishes -- operand rows in the ARRIVING CTA's own shared memory, made visible to the async proxy by
+  // the fence.proxy.async before it -- is read back by that same SM's tensor core, after the leader has seen the
+  // arrival and issued the MMA; nothing written here is read through another SM's generic loads.
+  asm volatile("mbarrier.arrive.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
 }
-// wait that also acquires what threads of the peer CTA released before arriving
+// wait on a barrier the peer CTA arrives on (CTA-scope acquire: the .acquire.cluster form invalidates L1 on every poll)
 __device__ __forceinline__ void mbar_wait_cluster(uint32_t bar, uint32_t parity) {
   asm volatile(
       "{\n"
       ".reg .pred P1;\n"
       "WAIT_LOOP_C:\n"
-      "mbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 P1, [%0], %1;\n"
+      "mbarrier.try_wait.parity.shared::cta.b64 P1, [%0], %1;\n"
       "@P1 bra DONE_C;\n"
       "bra WAIT_LOOP_C;\n"
       "DONE_C:\n"

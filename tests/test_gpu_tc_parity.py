@@ -53,12 +53,24 @@ def _compare(H, W, focal, c2w, *, ndc, near, far, lindisp, white):
         rgb16, _, acc16, ex16 = nk.render(H, W, focal, c2w=c2w[:3, :4], precision="fp16", **kw)
     acc_ref = ref["acc_fine"]
     assert float(acc_ref.std()) > 0.05, "degenerate scene"          # the test scene is not empty / not fog
-    e32 = maxdiff(rgb32, ref["rgb_fine"])
-    e16, a16 = maxdiff(rgb16, ref["rgb_fine"]), maxdiff(acc16, acc_ref)
-    c16 = maxdiff(ex16["rgb0"], ref["rgb_coarse"])
-    dpsnr, p32 = _psnr_delta(rgb16.cpu(), ref["rgb_fine"])
-    msg = "fp32 %.2e | fp16 rgb %.2e acc %.2e rgb0 %.2e | dPSNR %.4f dB at %.1f dB" % (e32, e16, a16, c16, dpsnr, p32)
+    # Conditioning.  raw2outputs gives the LAST sample of a ray the distance 1e10 (run_nerf.py:118-125), so its alpha is
+    # a step function of its raw sigma: 0 below zero, 1 above.  A random scene puts that sigma near zero on many rays
+    # (a trained one does not: the far plane is empty or solid), and there the reference is discontinuous in its own
+    # inputs -- any rounding flips acc between ~0.2 and 1.  The bound is asserted on the rays whose far-plane sigma is at
+    # least TAU away from zero in both passes of the oracle; the others must merely be finite.
+    TAU = 0.3
+    well = (ref["raw_coarse"][..., -1, 3].abs() > TAU) & (ref["raw_fine"][..., -1, 3].abs() > TAU)
+    frac = float(well.float().mean())
+    assert frac > 0.4, frac
+    wd = lambda a, b: maxdiff(a.cpu()[well], b[well])
+    e32 = wd(rgb32, ref["rgb_fine"])
+    e16, a16 = wd(rgb16, ref["rgb_fine"]), wd(acc16, acc_ref)
+    c16 = wd(ex16["rgb0"], ref["rgb_coarse"])
+    dpsnr, p32 = _psnr_delta(rgb16.cpu()[well], ref["rgb_fine"][well])
+    msg = "well-conditioned rays %.1f %% | fp32 %.2e | fp16 rgb %.2e acc %.2e rgb0 %.2e | dPSNR %.4f dB at %.1f dB" % (
+        100 * frac, e32, e16, a16, c16, dpsnr, p32)
     print(msg)
+    assert bool(torch.isfinite(rgb16).all()) and bool(torch.isfinite(rgb32).all())
     assert e32 <= 1e-3, msg
     assert e16 <= 1e-2 and a16 <= 1e-2 and c16 <= 1e-2, msg
     assert dpsnr <= 0.05, msg

@@ -162,6 +162,8 @@ def test_tc_backward_exact_given_saved_activations(case, n, S):
     check(lib().nb_mlp_record_layout(h, P, _ptr(ws), C.byref(xo), C.byref(xb), C.byref(do), C.byref(db)))
     nt = (P + 127) // 128
     X = _unswizzle(ws[xo.value: xo.value + nt * xb.value * 16384], nt, xb.value).double()
+    # blocks 0 / 1 are the encodings; activation blocks hold kActScale * h (a power of two: exact to undo)
+    X[:, 2:] /= float(lib().nb_mlp_activation_scale())
     blocks = lambda T, b0, nb: T[:, b0:b0 + nb].permute(0, 2, 1, 3).reshape(nt * 128, nb * 64)
     q = lambda k: sd[k].half().double().to(DEV)
     names = ([f"pts_linears.{i}" for i in range(64) if f"pts_linears.{i}.weight" in sd] if tf else
