@@ -29,8 +29,8 @@ def models(dev, seed=0):
     mc, mf = nk.NeRF().to(dev), nk.NeRF().to(dev)
     with torch.no_grad():       # a scene with structure (see tests/test_gpu_tc_parity.py)
         for m in (mc, mf):
-            m.alpha_linear.weight.mul_(30.0)
-            m.alpha_linear.bias.fill_(-0.2)
+            m.alpha_linear.weight.mul_(300.0)
+            m.alpha_linear.bias.fill_(-3.0)
             m.rgb_linear.weight.mul_(8.0)
     return mc, mf
 
