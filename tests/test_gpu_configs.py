@@ -77,7 +77,11 @@ def test_cfg3_wheel_pose_path_1280x720():
         assert torch.equal(torch.cat([p["rgb_map"] for p in parts]), rgb16)
         # the whole 60-pose video path through the public call (2 poses here), frames in host memory
         rgbs, disps = nk.render_path(poses[:2], (H, W, K), 32768, dict(kw, precision="fp16"))
-    assert rgbs.shape == (2, H, W, 3) and disps.shape == (2, H, W) and np.isfinite(rgbs).all()
+        rgbs32, _ = nk.render_path(poses[:2], (H, W, K), 32768, dict(kw, precision="fp32"))
+    assert rgbs.shape == (2, H, W, 3) and disps.shape == (2, H, W)
+    # NDC divides by the ray's z component: poses that look along the image plane give inf / NaN rays, which the
+    # reference propagates (SURVEY 8a difference 6); both precisions must propagate them to the same pixels
+    assert np.array_equal(np.isfinite(rgbs), np.isfinite(rgbs32)) and np.isfinite(rgbs).mean() > 0.5
 
 
 def _fern_scene():
