@@ -200,7 +200,8 @@ constexpr uint64_t kDescHiSw64 = ((uint64_t)1 << 16) | ((uint64_t)(512 >> 4) << 
 // ------------------------------------------------------------------------------------ the kernel
 __global__ void __launch_bounds__(kThreadsTc, 1)
 mlp_tc_kernel(const __grid_constant__ TcPlan plan, const unsigned char* __restrict__ wpk, const float* __restrict__ bias_g,
-              TcSrc src, long long n_points, float* __restrict__ raw, unsigned char* __restrict__ rec, int dbg) {
+              TcSrc src, long long n_points, float* __restrict__ raw, unsigned char* __restrict__ rec,
+              unsigned char* __restrict__ mrec, int dbg) {
   extern __shared__ __align__(1024) unsigned char smem_raw[];
   // carve (all tile regions 1024-byte aligned for SWIZZLE_128B)
   unsigned char* smem = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
@@ -459,6 +460,19 @@ mlp_tc_kernel(const __grid_constant__ TcPlan plan, const unsigned char* __restri
               mbar_arrive(smem_u32(bar_drain + t));
             }
             if (NB_DBG(dbg & 2)) { fence_async_smem(); mbar_arrive(smem_u32(bar_act + 4 * t + j)); continue; }
+            if (mrec != nullptr && relu) {
+              // train: 1-bit ReLU mask of this row's 64 pre-activations for the dgrad chain (8 B per row instead of the
+              // 128-byte activation row it used to re-read): element i of the block -> bit 31 - (i & 31) of word i >> 5,
+              // set where the accumulator's sign bit is clear (funnel shifts collect the sign bits, one per value)
+              uint32_t n0 = 0u, n1 = 0u;
+#pragma unroll
+              for (int i = 0; i < 32; ++i) {
+                n0 = __funnelshift_l(v[i], n0, 1);
+                n1 = __funnelshift_l(v[32 + i], n1, 1);
+              }
+              *reinterpret_cast<uint2*>(mrec + (((size_t)tile * (plan.rec_blocks - 2) + (st.rec_blk - 2 + j)) * kTileM + row) * 8) =
+                  make_uint2(~n0, ~n1);
+            }
             const uint32_t rp = smem_u32(act_t) + j * kBlockBytes + row * 128;
             if (st.alpha_dot) {
               const uint32_t wa = smem_u32(bias_s) + (plan.alpha_w_off + j * 64) * 4;
@@ -1071,6 +1085,7 @@ int tc_forward(const nb_model* m, const float* rays, int ray_stride, const float
   }
   const PackedBf16* p = m->packed;
   unsigned char* rec = nullptr;
+  unsigned char* mrec = nullptr;
   if (save_for_backward) {
     if (!p->bw_supported) {
       set_error("tensor-core backward does not support this graph (train it with NB_PREC_FP32)");
@@ -1082,6 +1097,7 @@ int tc_forward(const nb_model* m, const float* rays, int ray_stride, const float
       return NB_ERR_WORKSPACE;
     }
     rec = tc_train_xrec(p, ws, n_points);
+    mrec = tc_train_mrec(p, ws, n_points);
   }
   TcSrc src{rays, ray_stride, z_vals, n_samples > 0 ? n_samples : 1, pts, viewdirs, points_per_dir > 0 ? points_per_dir : 1};
   const int64_t n_tiles = ceil_div(n_points, kTileM);
@@ -1101,7 +1117,7 @@ int tc_forward(const nb_model* m, const float* rays, int ray_stride, const float
 #else
   const int dbg = 0;
 #endif
-  mlp_tc_kernel<<<grid, kThreadsTc, p->smem_bytes, stream>>>(p->plan, p->d_w, p->d_bias, src, (long long)n_points, raw, rec, dbg);
+  mlp_tc_kernel<<<grid, kThreadsTc, p->smem_bytes, stream>>>(p->plan, p->d_w, p->d_bias, src, (long long)n_points, raw, rec, mrec, dbg);
   NB_LAUNCHED();
   return NB_OK;
 }

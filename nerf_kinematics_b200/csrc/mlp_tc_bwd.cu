@@ -31,7 +31,7 @@
 namespace nb {
 
 constexpr int kThreadsBw = 224;   // W producer, MMA issuer, 4 epilogue warps, mask producer
-constexpr int kMaskRing = 3;
+constexpr int kMaskRing = 0;     // (the ReLU masks used to be 16 KB tiles of the X record streamed through a ring)
 constexpr int kThreadsWg = 192;   // producer, MMA issuer, 4 column-sum / epilogue warps
 constexpr int kWgMaxStages = 8;
 constexpr int kHalfBytes = 64 * 128;  // 64 points of a block
@@ -74,6 +74,7 @@ struct BwArgs {
   const float* d_raw;             // [n_points, 4]
   const unsigned* absmax_bits;
   const unsigned char* xrec;
+  const unsigned char* mrec;      // 1-bit ReLU masks written by the forward epilogue: [tile][rec_blocks - 2][128 rows] x 8 B
   unsigned char* drec;
   long long n_points;
   int rec_blocks, n_g_blocks;
@@ -168,24 +169,8 @@ mlp_tc_dgrad_kernel(const __grid_constant__ BwPlan plan, const BwArgs a) {
       }
     }
   } else if (warp == 6) {
-    // ============================ mask producer ============================
-    if (lane == 0) {
-      uint32_t slot = 0, phase = 0;
-      for (long long tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
-        const unsigned char* xt = a.xrec + (size_t)tile * a.rec_blocks * kBlockBytes;
-        for (int s = 0; s < plan.n_stages; ++s) {
-          const BwStage& st = plan.st[s];
-          if (st.mask_blk < 0) continue;
-          for (int j = 0; j < st.n_out; ++j) {
-            mbar_wait(smem_u32(m_empty + slot), phase ^ 1);
-            const uint32_t fb = smem_u32(m_full + slot);
-            mbar_expect_tx(fb, kBlockBytes);
-            bulk_g2s(smem_u32(mring + slot * kBlockBytes), xt + (size_t)(st.mask_blk + j) * kBlockBytes, kBlockBytes, fb);
-            if (++slot == kMaskRing) { slot = 0; phase ^= 1; }
-          }
-        }
-      }
-    }
+    // (this warp built the step program above; the ReLU masks are now 8 bytes per row read straight from the 1-bit
+    // record by the epilogue threads, so there is no mask tile to stream)
   } else if (warp == 1) {
     // ============================ MMA issuer ============================
     // Whole warp, warp-uniform control flow over a step program in shared memory (one entry per K-block); only the
@@ -263,7 +248,6 @@ mlp_tc_dgrad_kernel(const __grid_constant__ BwPlan plan, const BwArgs a) {
     const uint32_t lane_addr = ((uint32_t)(q * 32)) << 16;
     const float scale = grad_scale_from(*a.absmax_bits);
     uint32_t acc_phase[2] = {0, 0};
-    uint32_t mslot = 0, mphase = 0;
     const int sw = row & 7;
     for (long long tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
       {
@@ -290,17 +274,27 @@ mlp_tc_dgrad_kernel(const __grid_constant__ BwPlan plan, const BwArgs a) {
         tc_fence_after();
         const uint32_t t_main = tmem_base + lane_addr + buf * 256;
         const bool masked = st.mask_blk >= 0;
+        const uint2* mrow = reinterpret_cast<const uint2*>(a.mrec) +
+                            ((size_t)tile * (a.rec_blocks - 2) + (masked ? st.mask_blk - 2 : 0)) * kTileM + row;
         for (int j = 0; j < st.n_out; ++j) {
           uint32_t v[64];
+          uint2 mk = make_uint2(0xffffffffu, 0xffffffffu);
+          if (masked) mk = __ldg(mrow + (size_t)j * kTileM);   // requested before the accumulator load is waited for
           NB_TMEM_LD32(t_main + j * 64, v);
           {
             uint32_t* v2 = v + 32;
             NB_TMEM_LD32(t_main + j * 64 + 32, v2);
           }
-          if (masked) mbar_wait(smem_u32(m_full + mslot), mphase);
           tc_wait_ld();
           unsigned char* rp = gact + j * kBlockBytes + row * 128;
-          const unsigned char* mp = mring + mslot * kBlockBytes + row * 128;
+          if (masked) {
+            // element i of the block passes where bit 31 - (i & 31) of mask word i >> 5 is set (forward epilogue)
+#pragma unroll
+            for (int i = 0; i < 32; ++i) {
+              if (!(mk.x & (0x80000000u >> i))) v[i] = 0u;
+              if (!(mk.y & (0x80000000u >> i))) v[32 + i] = 0u;
+            }
+          }
 #pragma unroll
           for (int c = 0; c < 8; ++c) {
             uint4 pk;
@@ -308,24 +302,11 @@ mlp_tc_dgrad_kernel(const __grid_constant__ BwPlan plan, const BwArgs a) {
             pk.y = pack_h2(__uint_as_float(v[8 * c + 2]), __uint_as_float(v[8 * c + 3]), false);
             pk.z = pack_h2(__uint_as_float(v[8 * c + 4]), __uint_as_float(v[8 * c + 5]), false);
             pk.w = pack_h2(__uint_as_float(v[8 * c + 6]), __uint_as_float(v[8 * c + 7]), false);
-            const int off = (c ^ sw) << 4;
-            if (masked) {
-              const uint4 m = *reinterpret_cast<const uint4*>(mp + off);
-              const __half2 zero = __float2half2_rn(0.0f);
-              pk.x &= __hgt2_mask(*reinterpret_cast<const __half2*>(&m.x), zero);
-              pk.y &= __hgt2_mask(*reinterpret_cast<const __half2*>(&m.y), zero);
-              pk.z &= __hgt2_mask(*reinterpret_cast<const __half2*>(&m.z), zero);
-              pk.w &= __hgt2_mask(*reinterpret_cast<const __half2*>(&m.w), zero);
-            }
-            *reinterpret_cast<uint4*>(rp + off) = pk;
+            *reinterpret_cast<uint4*>(rp + ((c ^ sw) << 4)) = pk;
           }
           tc_fence_before();
           fence_async_smem();
           mbar_arrive(smem_u32(bar_act + j));
-          if (masked) {
-            mbar_arrive(smem_u32(m_empty + mslot));
-            if (++mslot == kMaskRing) { mslot = 0; mphase ^= 1; }
-          }
         }
       }
     }
@@ -771,7 +752,7 @@ int bw_setup(nb_model* m, cudaStream_t stream) {
 }
 
 struct BwLayout {
-  size_t off_scale = 0, off_xrec = 0, off_drec = 0, off_pw = 0, off_pb = 0, total = 0;
+  size_t off_scale = 0, off_xrec = 0, off_mrec = 0, off_drec = 0, off_pw = 0, off_pb = 0, total = 0;
   int64_t n_tiles = 0;
   int max_ctas = 0;
 };
@@ -783,6 +764,7 @@ static BwLayout bw_layout(const PackedBf16* p, int64_t n_points) {
   auto take = [&](size_t bytes) { size_t o = off; off += (size_t)round_up((int64_t)bytes, 1024); return o; };
   L.off_scale = take(256);
   L.off_xrec = take((size_t)L.n_tiles * p->plan.rec_blocks * kBlockBytes);
+  L.off_mrec = take((size_t)L.n_tiles * (p->plan.rec_blocks - 2) * kTileM * 8);
   L.off_drec = take((size_t)L.n_tiles * p->bw.drec_blocks * kBlockBytes);
   L.off_pw = take((size_t)L.max_ctas * kPartFloats * sizeof(float));
   L.off_pb = take((size_t)L.max_ctas * 4 * 256 * sizeof(float));
@@ -790,6 +772,10 @@ static BwLayout bw_layout(const PackedBf16* p, int64_t n_points) {
   return L;
 }
 
+unsigned char* tc_train_mrec(const PackedBf16* p, void* ws, int64_t n_points) {
+  unsigned char* base = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(ws) + 1023) & ~(uintptr_t)1023);
+  return base + bw_layout(p, n_points).off_mrec;
+}
 size_t tc_train_workspace_bytes(const PackedBf16* p, int64_t n_points) { return bw_layout(p, n_points).total + 1024; }
 unsigned char* tc_train_xrec(const PackedBf16* p, void* ws, int64_t n_points) {
   unsigned char* base = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(ws) + 1023) & ~(uintptr_t)1023);
@@ -858,6 +844,7 @@ int tc_backward(const nb_model* m, int64_t n_points, float* d_raw, void* ws, siz
   ba.d_raw = d_raw;
   ba.absmax_bits = absmax;
   ba.xrec = base + L.off_xrec;
+  ba.mrec = base + L.off_mrec;
   ba.drec = base + L.off_drec;
   ba.n_points = n_points;
   ba.rec_blocks = p->plan.rec_blocks;

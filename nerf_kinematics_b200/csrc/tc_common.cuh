@@ -29,7 +29,7 @@ constexpr float kInvActScale = 32.0f;
 
 constexpr int kMaxStages = 14;
 constexpr int kMaxKB = 6;
-constexpr int kRing = 3;
+constexpr int kRing = 4;   // dgrad weight ring (4 x 32 KB since the mask ring is gone)
 constexpr int kTileM = 128;
 constexpr int kBlockBytes = kTileM * 128;  // one 128-row x 64-element 16-bit K-block, SWIZZLE_128B
 enum { SRC_ENCX = 4, SRC_ENCD = 5, SRC_DRAW = 6, SRC_BIAS = 7 };
@@ -392,5 +392,6 @@ int bw_setup(nb_model* m, cudaStream_t stream);  // plans + buffers of the backw
 void bw_free(PackedBf16* p);
 size_t tc_train_workspace_bytes(const PackedBf16* p, int64_t n_points);
 unsigned char* tc_train_xrec(const PackedBf16* p, void* ws, int64_t n_points);  // X record inside the workspace
+unsigned char* tc_train_mrec(const PackedBf16* p, void* ws, int64_t n_points);  // 1-bit ReLU mask record (8 B per row and block)
 
 }  // namespace nb
