@@ -454,7 +454,7 @@ mlp_tc_kernel(const __grid_constant__ TcPlan plan, const unsigned char* __restri
               uint32_t* v2 = v + 32;
               NB_TMEM_LD32(t_main + j * 64 + 32, v2);
             }
-            tc_wait_ld();
+            NB_TMEM_WAIT64(v);
             if (j + 2 >= nblk) {  // last accumulator read of this stage: hand the TMEM columns back
               tc_fence_before();
               mbar_arrive(smem_u32(bar_drain + t));
@@ -799,7 +799,7 @@ mlp_tc2_kernel(const __grid_constant__ TcPlan plan, const unsigned char* __restr
               uint32_t* v2p = v + 32;
               NB_TMEM_LD32(t_main + j * 64 + 32, v2p);
             }
-            tc_wait_ld();
+            NB_TMEM_WAIT64(v);
             if (j + 2 >= nblk) {
               tc_fence_before();
               __syncwarp();

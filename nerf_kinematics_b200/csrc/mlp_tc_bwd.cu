@@ -269,23 +269,32 @@ mlp_tc_dgrad_kernel(const __grid_constant__ BwPlan plan, const BwArgs a) {
       for (int s = 0; s < plan.n_stages; ++s) {
         const BwStage& st = plan.st[s];
         const int buf = s & 1;
+        // this stage's ReLU masks (8 B per row and 64-column block) are requested before the wait for the stage's
+        // accumulator: the MMAs in flight hide the HBM latency
+        const bool masked = st.mask_blk >= 0;
+        const uint2* mrow = reinterpret_cast<const uint2*>(a.mrec) +
+                            ((size_t)tile * (a.rec_blocks - 2) + (masked ? st.mask_blk - 2 : 0)) * kTileM + row;
+        uint2 mk0, mk1, mk2, mk3;
+        mk0 = mk1 = mk2 = mk3 = make_uint2(0xffffffffu, 0xffffffffu);
+        if (masked) {
+          mk0 = __ldg(mrow);
+          if (st.n_out > 1) mk1 = __ldg(mrow + kTileM);
+          if (st.n_out > 2) mk2 = __ldg(mrow + 2 * kTileM);
+          if (st.n_out > 3) mk3 = __ldg(mrow + 3 * kTileM);
+        }
         mbar_wait(smem_u32(bar_acc + buf), acc_phase[buf]);
         acc_phase[buf] ^= 1;
         tc_fence_after();
         const uint32_t t_main = tmem_base + lane_addr + buf * 256;
-        const bool masked = st.mask_blk >= 0;
-        const uint2* mrow = reinterpret_cast<const uint2*>(a.mrec) +
-                            ((size_t)tile * (a.rec_blocks - 2) + (masked ? st.mask_blk - 2 : 0)) * kTileM + row;
         for (int j = 0; j < st.n_out; ++j) {
           uint32_t v[64];
-          uint2 mk = make_uint2(0xffffffffu, 0xffffffffu);
-          if (masked) mk = __ldg(mrow + (size_t)j * kTileM);   // requested before the accumulator load is waited for
+          const uint2 mk = j == 0 ? mk0 : j == 1 ? mk1 : j == 2 ? mk2 : mk3;
           NB_TMEM_LD32(t_main + j * 64, v);
           {
             uint32_t* v2 = v + 32;
             NB_TMEM_LD32(t_main + j * 64 + 32, v2);
           }
-          tc_wait_ld();
+          NB_TMEM_WAIT64(v);
           unsigned char* rp = gact + j * kBlockBytes + row * 128;
           if (masked) {
             // element i of the block passes where bit 31 - (i & 31) of mask word i >> 5 is set (forward epilogue)

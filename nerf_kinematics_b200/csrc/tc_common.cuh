@@ -329,6 +329,16 @@ __device__ __forceinline__ void tc_wait_ld() { asm volatile("tcgen05.wait::ld.sy
         "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])                   \
       : "r"(taddr))
 
+// tcgen05.wait::ld that the compiler sees as (re)defining the 64 registers of two x32 loads: plain C++ arithmetic on those
+// registers (mask bit packing, conditional zeroing) would otherwise be free to move above the wait -- only asm volatile
+// statements are ordered with respect to each other -- and read them before the asynchronous load has landed.
+#define NB_R8(v, o) "+r"(v[o]), "+r"(v[o + 1]), "+r"(v[o + 2]), "+r"(v[o + 3]), "+r"(v[o + 4]), "+r"(v[o + 5]), "+r"(v[o + 6]), "+r"(v[o + 7])
+#define NB_TMEM_WAIT64(v)                                                                                           \
+  do {                                                                                                              \
+    asm volatile("tcgen05.wait::ld.sync.aligned;" : NB_R8(v, 0), NB_R8(v, 8), NB_R8(v, 16), NB_R8(v, 24)::"memory"); \
+    asm volatile("" : NB_R8(v, 32), NB_R8(v, 40), NB_R8(v, 48), NB_R8(v, 56)::"memory");                          \
+  } while (0)
+
 __device__ __forceinline__ void tmem_ld4(uint32_t taddr, uint32_t (&v)[4]) {
   asm volatile("tcgen05.ld.sync.aligned.32x32b.x4.b32 {%0,%1,%2,%3}, [%4];"
                : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3])
