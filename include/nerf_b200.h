@@ -182,6 +182,13 @@ float nb_mlp_activation_scale(void);
 int nb_mlp_record_layout(const nb_model_t* m, int64_t n_points, const void* workspace, int64_t* xrec_offset,
                          int* xrec_blocks, int64_t* drec_offset, int* drec_blocks);
 
+/* The 1-bit ReLU mask record of the same workspace: per 128-point tile and per ACTIVATION block b (X-record block b + 2),
+ * 128 rows x 8 bytes; element i of the row's 64 pre-activations is bit 31 - (i & 31) of 32-bit word i >> 5, set where the
+ * fp32 pre-activation is positive (its sign bit clear) -- what the dgrad chain multiplies by; a pre-activation too small
+ * for the 16-bit X record (< 1e-6) still passes its gradient, as it does in the fp32 reference. */
+int nb_mlp_mask_record_layout(const nb_model_t* m, int64_t n_points, const void* workspace, int64_t* mrec_offset,
+                              int* mrec_blocks);
+
 /* ---------------------------------------------------------------- a9 compositing
  * raw2outputs (TF run_nerf.py:93-163) == volume_render_radiance_field (PT volume_rendering_utils.py:6-53).
  * noise ([n,S], already multiplied by raw_noise_std) may be NULL.  depth / weights may be NULL. */

@@ -73,6 +73,7 @@ SIGNATURES = {
     "nb_mlp_forward_points": (i32, [p, i32, p, p, i64, i32, p, p, sz, p]),
     "nb_mlp_backward": (i32, [p, i32, i64, p, p, sz, p, p]),
     "nb_mlp_activation_scale": (f32, []),
+    "nb_mlp_mask_record_layout": (i32, [p, i64, p, C.POINTER(i64), C.POINTER(i32)]),
     "nb_mlp_record_layout": (i32, [p, i64, p, C.POINTER(i64), C.POINTER(i32), C.POINTER(i64), C.POINTER(i32)]),
     "nb_composite": (i32, [p, p, p, i32, i64, i32, p, i32, p, p, p, p, p, p]),
     "nb_composite_backward": (i32, [p, p, p, i32, i64, i32, p, i32, p, p, p, p, p, p]),

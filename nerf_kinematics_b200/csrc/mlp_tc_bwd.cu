@@ -901,3 +901,16 @@ extern "C" int nb_mlp_record_layout(const nb_model_t* m, int64_t n_points, const
   if (drec_blocks) *drec_blocks = m->packed->bw.drec_blocks;
   return NB_OK;
 }
+
+extern "C" int nb_mlp_mask_record_layout(const nb_model_t* m, int64_t n_points, const void* workspace, int64_t* mrec_offset,
+                                         int* mrec_blocks) {
+  using namespace nb;
+  NB_REQUIRE(m != nullptr && m->packed != nullptr && m->packed->bw_supported,
+             "nb_mlp_mask_record_layout: model is not packed for the tensor-core train path");
+  const BwLayout L = bw_layout(m->packed, n_points);
+  const uintptr_t w = reinterpret_cast<uintptr_t>(workspace);
+  const uintptr_t base = (w + 1023) & ~(uintptr_t)1023;
+  if (mrec_offset) *mrec_offset = (int64_t)(base - w + L.off_mrec);
+  if (mrec_blocks) *mrec_blocks = m->packed->plan.rec_blocks - 2;
+  return NB_OK;
+}

@@ -164,6 +164,15 @@ def test_tc_backward_exact_given_saved_activations(case, n, S):
     X = _unswizzle(ws[xo.value: xo.value + nt * xb.value * 16384], nt, xb.value).double()
     # blocks 0 / 1 are the encodings; activation blocks hold kActScale * h (a power of two: exact to undo)
     X[:, 2:] /= float(lib().nb_mlp_activation_scale())
+    # the ReLU masks the dgrad chain used: 1 bit per pre-activation, taken from the fp32 accumulator's sign (a positive
+    # value too small for the 16-bit record still passes its gradient, like in the fp32 reference)
+    mo, mb = C.c_int64(), C.c_int()
+    check(lib().nb_mlp_mask_record_layout(h, P, _ptr(ws), C.byref(mo), C.byref(mb)))
+    assert mb.value == xb.value - 2
+    words = ws[mo.value: mo.value + nt * mb.value * 128 * 8].view(torch.int32).view(nt, mb.value, 128, 2).to(torch.int64) & 0xFFFFFFFF
+    sh = (31 - torch.arange(32, device=DEV)).view(1, 1, 1, 1, 32)
+    M = ((words.unsqueeze(-1) >> sh) & 1).reshape(nt, mb.value, 128, 64).double()     # [tile, block, row, element]
+    mask = lambda b0, nb: blocks(M, b0 - 2, nb) > 0                                   # by X-record block index
     blocks = lambda T, b0, nb: T[:, b0:b0 + nb].permute(0, 2, 1, 3).reshape(nt * 128, nb * 64)
     q = lambda k: sd[k].half().double().to(DEV)
     names = ([f"pts_linears.{i}" for i in range(64) if f"pts_linears.{i}.weight" in sd] if tf else
@@ -183,10 +192,10 @@ def test_tc_backward_exact_given_saved_activations(case, n, S):
         fb, dbk = fw // 64, (W // 2) // 64
         feat, dirh = blocks(X, 2 + wb * D, fb), blocks(X, 2 + wb * D + fb, dbk)
         assert xb.value == 2 + wb * D + fb + dbk
-        dz_dir = (dr[:, :3] @ q(n_rgb + ".weight")) * (dirh > 0)
+        dz_dir = (dr[:, :3] @ q(n_rgb + ".weight")) * mask(2 + wb * D + fb, dbk)
         dz_feat = dz_dir @ q(n_dir + ".weight")[:, :fw]
         if not tf:
-            dz_feat = dz_feat * (feat > 0)
+            dz_feat = dz_feat * mask(2 + wb * D, fb)
         dz = dz_feat @ q(n_feat + ".weight") + dr[:, 3:4] * q(n_alpha + ".weight")
         ref[n_rgb + ".weight"], ref[n_rgb + ".bias"] = dr[:, :3].t() @ dirh, dr[:, :3].sum(0)
         ref[n_alpha + ".weight"], ref[n_alpha + ".bias"] = dr[:, 3:4].t() @ hs[-1], dr[:, 3:4].sum(0)
@@ -196,7 +205,7 @@ def test_tc_backward_exact_given_saved_activations(case, n, S):
         dz = dr @ q("output_linear.weight")
         ref["output_linear.weight"], ref["output_linear.bias"] = dr.t() @ hs[-1], dr.sum(0)
     if relu_after(D - 1):
-        dz = dz * (hs[-1] > 0)
+        dz = dz * mask(2 + wb * (D - 1), wb)
     for i in range(D - 1, -1, -1):
         cat = i >= 1 and (i - 1) in skips
         xin = encx if i == 0 else (torch.cat([encx, hs[i - 1]], 1) if cat else hs[i - 1])
@@ -205,7 +214,7 @@ def test_tc_backward_exact_given_saved_activations(case, n, S):
             off = 63 if cat else 0
             dz = dz @ q(names[i] + ".weight")[:, off:off + W]
             if relu_after(i - 1):
-                dz = dz * (hs[i - 1] > 0)
+                dz = dz * mask(2 + wb * (i - 1), wb)
     bad = []
     for key, shape, off in m._layout:
         cnt = 1
