@@ -117,15 +117,8 @@ struct TcSrc {
 // [kChunk0, kChunk0 + kChunks) of them as row `row` of a SWIZZLE_128B K-block.  Higher octaves by the double-angle
 // recurrence from one accurate sincosf per component: the absolute error doubles per octave (<= 2^9 * 6e-8), far
 // below the fp16 quantum (4.9e-4) of the stored value.
-// streaming 16-byte store of a record chunk (written once, read once by a later kernel: keep it out of the way in L2)
-__device__ __forceinline__ void stg_rec(unsigned char* p, const uint4& v) {
-  asm volatile("st.global.cs.v4.b32 [%0], {%1,%2,%3,%4};" ::"l"(p), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
-}
-
-// grow (train): the same 128-byte swizzled row in the per-tile X record, or null
 template <int kChunk0, int kChunks>
-__device__ __forceinline__ void encode_row(unsigned char* block, int row, float x0, float x1, float x2, int L,
-                                           unsigned char* grow = nullptr) {
+__device__ __forceinline__ void encode_row(unsigned char* block, int row, float x0, float x1, float x2, int L) {
   float s[3], c[3];
   sincosf(x0, &s[0], &c[0]);
   sincosf(x1, &s[1], &c[1]);
@@ -154,7 +147,6 @@ __device__ __forceinline__ void encode_row(unsigned char* block, int row, float 
     pk.z = pack_h2(ch[8 * q + 4], ch[8 * q + 5], false);
     pk.w = pack_h2(ch[8 * q + 6], ch[8 * q + 7], false);
     *reinterpret_cast<uint4*>(rp + ((q ^ (row & 7)) << 4)) = pk;
-    if (grow != nullptr) stg_rec(grow + ((q ^ (row & 7)) << 4), pk);
   }
 }
 
@@ -172,7 +164,7 @@ __device__ __forceinline__ void sts_u4(uint32_t saddr, const uint4& v) {
 // row's 128-byte line at rp; kAlpha also accumulates <activation, alpha weights> in fp32
 template <bool kAlpha, int kRelu = -1>  // kRelu: 0 / 1 = compile-time activation choice, -1 = the run-time flag
 __device__ __forceinline__ void epi_convert32(const uint32_t (&v)[64], int c0, uint32_t rp, uint32_t wa, int sw,
-                                              bool relu_rt, float& adot, unsigned char* grow = nullptr) {
+                                              bool relu_rt, float& adot) {
   const bool relu = kRelu < 0 ? relu_rt : kRelu != 0;
 #pragma unroll
   for (int c = 0; c < 4; ++c) {
@@ -195,9 +187,6 @@ __device__ __forceinline__ void epi_convert32(const uint32_t (&v)[64], int c0, u
     pk.z = pack_h2(a4, a5, relu);
     pk.w = pack_h2(a6, a7, relu);
     sts_u4(rp + ((((c0 >> 3) + c) ^ sw) << 4), pk);
-    // train: the X record gets the same bytes straight from the registers (fire and forget: nothing has to be waited
-    // for before the block is overwritten, and the bulk-copy engine no longer re-reads it from shared memory)
-    if (grow != nullptr) stg_rec(grow + ((((c0 >> 3) + c) ^ sw) << 4), pk);
   }
 }
 
@@ -332,6 +321,8 @@ mlp_tc_kernel(const __grid_constant__ TcPlan plan, const unsigned char* __restri
     const uint32_t enc_off = plan.n_act_blocks * kBlockBytes;
     const uint32_t d_tmem = tmem_base + t * 256;
     const int n_steps = plan.n_steps;
+    const size_t rec_stride = (size_t)plan.rec_blocks * kBlockBytes;
+    const uint64_t pol_rec = l2_evict_first();
     for (long long tile0 = tile_begin; tile0 < tile_end; tile0 += 2) {
       if (tile0 + t >= tile_end) {
         // trailing single tile: this issuer only keeps the ring's two-commit protocol going
@@ -343,9 +334,16 @@ mlp_tc_kernel(const __grid_constant__ TcPlan plan, const unsigned char* __restri
         }
         break;
       }
-      // (train: the epilogue warps write every operand block to the per-tile X record as they produce it)
+      // train: every operand block is also written to the per-tile X record, in the exact swizzled image the
+      // backward kernels load (K-major for recompute-free dgrad masks, MN-major operand of the wgrad MMAs)
+      unsigned char* rec_t = rec ? rec + (size_t)(tile0 + t) * rec_stride : nullptr;
       mbar_wait(bar_enc_s, ph_enc);
       ph_enc ^= 1;
+      if (rec && elect_one()) {
+        bulk_s2g_hint(rec_t, act_s + enc_off, kBlockBytes, pol_rec);
+        bulk_commit();
+      }
+      __syncwarp();
       uint4 e = prog[0];
       for (int i = 0; i < n_steps; ++i) {
         const uint4 en = prog[i + 1 < n_steps ? i + 1 : i];  // prefetch
@@ -359,6 +357,11 @@ mlp_tc_kernel(const __grid_constant__ TcPlan plan, const unsigned char* __restri
             mbar_wait(bar_encd_s, ph_encd);
             ph_encd ^= 1;
           }
+          if (rec && elect_one()) {
+            bulk_s2g_hint(rec_t + (size_t)e.w * kBlockBytes, act_s + (e.x & ~127u), kBlockBytes, pol_rec);
+            bulk_commit();
+          }
+          __syncwarp();
         }
         if ((fl & PF_FIRST) && armed) {  // the previous stage's epilogue has read this tile's accumulator out
           mbar_wait(bar_drain_s, ph_drain);
@@ -373,13 +376,18 @@ mlp_tc_kernel(const __grid_constant__ TcPlan plan, const unsigned char* __restri
           if (!(fl & PF_BIAS)) tc_mma(d_tmem, a_desc, b_desc, e.y, (fl & PF_ACC) ? 1u : 0u);
           tc_mma(d_tmem, a_desc + 2, b_desc + 2, e.y, 1u);
           tc_commit(bar_empty_s + 8 * slot);  // (1 of 2 arrivals) frees the ring slot when these MMAs have read it
-          if (fl & PF_LAST) tc_commit(bar_acc_s);  // accumulator of this stage complete
+          if (fl & PF_LAST) {
+            if (rec) bulk_wait_read0();  // record stores have read the blocks this stage's epilogue overwrites
+            tc_commit(bar_acc_s);        // accumulator of this stage complete
+          }
         }
         __syncwarp();
         if (++slot == kFwdRing) { slot = 0; phase ^= 1; }
         e = en;
       }
     }
+    if (rec && elect_one()) bulk_wait0();
+    __syncwarp();
   } else if (warp >= 4) {
     // ============================ epilogue warps (thread == row) ============================
     const int e = warp - 4;
@@ -399,9 +407,6 @@ mlp_tc_kernel(const __grid_constant__ TcPlan plan, const unsigned char* __restri
       long long p = tile * kTileM + row;
       const bool in_range = p < n_points;
       if (!in_range) p = n_points - 1;
-      // train: this tile's X record ([encx, encd, activations of every stage] x 16 KB, the exact swizzled images the
-      // wgrad kernel loads as MN-major operands); every thread writes the chunks of its own row
-      unsigned char* rec_t = rec ? rec + (size_t)tile * plan.rec_blocks * kBlockBytes : nullptr;
       // ---- positional encoding of this row's point (the two parities write 4 chunks of the row each)
       float v0 = 0.f, v1 = 0.f, v2 = 0.f;
       {
@@ -421,8 +426,8 @@ mlp_tc_kernel(const __grid_constant__ TcPlan plan, const unsigned char* __restri
             v0 = vv[0]; v1 = vv[1]; v2 = vv[2];
           }
         }
-        if (par == 0) encode_row<0, 4>(enc_t, row, x0, x1, x2, plan.Lx, rec_t ? rec_t + row * 128 : nullptr);
-        else encode_row<4, 4>(enc_t, row, x0, x1, x2, plan.Lx, rec_t ? rec_t + row * 128 : nullptr);
+        if (par == 0) encode_row<0, 4>(enc_t, row, x0, x1, x2, plan.Lx);
+        else encode_row<4, 4>(enc_t, row, x0, x1, x2, plan.Lx);
       }
       fence_async_smem();
       mbar_arrive(smem_u32(bar_enc + t));
@@ -469,17 +474,16 @@ mlp_tc_kernel(const __grid_constant__ TcPlan plan, const unsigned char* __restri
                   make_uint2(~n0, ~n1);
             }
             const uint32_t rp = smem_u32(act_t) + j * kBlockBytes + row * 128;
-            unsigned char* grow = rec_t ? rec_t + (size_t)(st.rec_blk + j) * kBlockBytes + row * 128 : nullptr;
             if (st.alpha_dot) {
               const uint32_t wa = smem_u32(bias_s) + (plan.alpha_w_off + j * 64) * 4;
-              epi_convert32<true>(v, 0, rp, wa, sw, relu, adot, grow);
-              epi_convert32<true>(v, 32, rp, wa, sw, relu, adot, grow);
+              epi_convert32<true>(v, 0, rp, wa, sw, relu, adot);
+              epi_convert32<true>(v, 32, rp, wa, sw, relu, adot);
             } else if (relu) {  // the common case without a branch per 16-byte chunk
-              epi_convert32<false, 1>(v, 0, rp, 0u, sw, true, adot, grow);
-              epi_convert32<false, 1>(v, 32, rp, 0u, sw, true, adot, grow);
+              epi_convert32<false, 1>(v, 0, rp, 0u, sw, true, adot);
+              epi_convert32<false, 1>(v, 32, rp, 0u, sw, true, adot);
             } else {
-              epi_convert32<false, 0>(v, 0, rp, 0u, sw, false, adot, grow);
-              epi_convert32<false, 0>(v, 32, rp, 0u, sw, false, adot, grow);
+              epi_convert32<false, 0>(v, 0, rp, 0u, sw, false, adot);
+              epi_convert32<false, 0>(v, 32, rp, 0u, sw, false, adot);
             }
             fence_async_smem();
             mbar_arrive(smem_u32(bar_act + 4 * t + j));
@@ -488,7 +492,7 @@ mlp_tc_kernel(const __grid_constant__ TcPlan plan, const unsigned char* __restri
           if (st.write_encd && par == 1) {
             // every MMA reading the position encoding has completed (bar_acc of this stage): the block now
             // becomes the direction encoding for the view-dependent layer
-            encode_row<0, 8>(enc_t, row, v0, v1, v2, plan.Ld, rec_t ? rec_t + kBlockBytes + row * 128 : nullptr);
+            encode_row<0, 8>(enc_t, row, v0, v1, v2, plan.Ld);
             fence_async_smem();
             mbar_arrive(smem_u32(bar_encd + t));
           }
