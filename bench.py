@@ -204,6 +204,31 @@ def _profiled_traffic(fname):
         return None
 
 
+def _profiled_traffic_backward():
+    """DRAM bytes (read + write) of the fine pass's dgrad + wgrad launches from the committed ncu list of one train step
+    (profiles/r2_train_kernels_ncu.csv, the section captured after the 1-bit masks); None if absent."""
+    try:
+        unit = {"Gbyte": 1e9, "Mbyte": 1e6, "Kbyte": 1e3, "byte": 1.0}
+        lines = open(os.path.join(ROOT, "profiles", "r2_train_kernels_ncu.csv")).read().split("# AFTER")[1].splitlines()[1:]
+        launches, cur = [], None
+        for ln in lines:
+            k, m, u, v = ln.split(",")[:4]
+            if cur is None or m in cur["seen"] or k != cur["k"]:
+                cur = {"k": k, "t": 0.0, "b": 0.0, "seen": set()}
+                launches.append(cur)
+            cur["seen"].add(m)
+            if m == "gpu__time_duration.sum":
+                cur["t"] = float(v)
+            elif m.startswith("dram__bytes"):
+                cur["b"] += float(v) * unit[u]
+        tot = 0.0
+        for name in ("mlp_tc_dgrad", "mlp_tc_wgrad"):
+            tot += max((l for l in launches if l["k"].startswith(name)), key=lambda l: l["t"])["b"]
+        return tot or None
+    except Exception:
+        return None
+
+
 def _events_time(fn, reps, warm=3):
     for _ in range(warm):
         fn()
@@ -519,7 +544,7 @@ def run_train(args):
             # the step's own dominant launch: the backward (dgrad chain + wgrad) of the fine pass
             out["roofline"] = {"bound": "tensor", "kernel": "train step backward of the fine pass (dgrad chain + wgrad + reduce), %d points" % tk["points"],
                                "achieved": tk["backward_tflops"], "peak": peak, "unit": "TFLOP/s",
-                               "frac": tk["backward_tflops"] / peak, "traffic": _profiled_traffic("r2_backward_kernels_ncu_full.csv"),
+                               "frac": tk["backward_tflops"] / peak, "traffic": _profiled_traffic_backward(),
                                "peak_source": pk["source"], "ms_per_launch": tk["backward_ms"],
                                "step_frac_of_tensor_peak": step_frac}
             out["roofline_kernels"] = {
