@@ -212,7 +212,7 @@ def _profiled_traffic_backward():
         lines = open(os.path.join(ROOT, "profiles", "r2_train_kernels_ncu.csv")).read().split("# AFTER")[1].splitlines()[1:]
         launches, cur = [], None
         for ln in lines:
-            k, m, u, v = ln.split(",")[:4]
+            k, m, u, v = ln.rsplit(",", 3)
             if cur is None or m in cur["seen"] or k != cur["k"]:
                 cur = {"k": k, "t": 0.0, "b": 0.0, "seen": set()}
                 launches.append(cur)
