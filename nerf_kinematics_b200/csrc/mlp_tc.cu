@@ -1124,12 +1124,18 @@ int tc_forward(const nb_model* m, const float* rays, int ray_stride, const float
 
 }  // namespace nb
 
+namespace nb { extern int g_bwd_sm_reserve; }
 extern "C" float nb_mlp_activation_scale(void) { return nb::kActScale; }
 
 extern "C" int nb_set_option(const char* name, int value) {
   using namespace nb;
   NB_REQUIRE(name != nullptr, "nb_set_option: null name");
   if (strcmp(name, "fwd_2cta") == 0) return set_fwd_2cta(value);
+  if (strcmp(name, "bwd_sm_reserve") == 0) {
+    const int old = g_bwd_sm_reserve;
+    g_bwd_sm_reserve = value < 0 ? 0 : (value > 64 ? 64 : value);
+    return old;
+  }
   set_error("nb_set_option: unknown option '%s'", name);
   return NB_ERR_INVALID;
 }

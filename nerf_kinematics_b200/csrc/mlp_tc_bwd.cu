@@ -63,6 +63,12 @@ __global__ void pack_weights_t_kernel(const float* __restrict__ params, const Pa
   pack_weights_t_body(params, segs[blockIdx.y], out, blockIdx.x * blockDim.x + threadIdx.x);
 }
 
+// SMs the persistent backward kernels leave free (nb_set_option("bwd_sm_reserve")): in the data-parallel step the fine
+// network's gradient all-reduce is enqueued on NCCL's stream while the coarse network's backward runs; both backward
+// kernels hold one 215 KB CTA on every SM, so NCCL's CTAs could not become resident until a backward kernel retired.
+int g_bwd_sm_reserve = 0;
+static int bwd_sms() { return std::max(8, sm_count() - g_bwd_sm_reserve); }
+
 // ------------------------------------------------------------------------------------ dgrad chain
 // flags of the dgrad MMA issuer's step program (bits 0-1: gradient block to wait for)
 enum : uint32_t { BF_WAIT_ACT = 4u, BF_K1 = 8u, BF_ACC = 16u, BF_LAST = 32u, BF_BUF1 = 64u };
@@ -858,7 +864,7 @@ int tc_backward(const nb_model* m, int64_t n_points, float* d_raw, void* ws, siz
   ba.n_points = n_points;
   ba.rec_blocks = p->plan.rec_blocks;
   ba.n_g_blocks = p->n_g_blocks;
-  const int grid = (int)std::min<int64_t>(L.n_tiles, sm_count());
+  const int grid = (int)std::min<int64_t>(L.n_tiles, bwd_sms());
   mlp_tc_dgrad_kernel<<<grid, kThreadsBw, p->bw_smem_bytes, stream>>>(p->bw, ba);
   NB_LAUNCHED();
   WgArgs wa{};
@@ -869,7 +875,7 @@ int tc_backward(const nb_model* m, int64_t n_points, float* d_raw, void* ws, siz
   wa.n_tiles = L.n_tiles;
   wa.rec_blocks = p->plan.rec_blocks;
   wa.drec_blocks = p->bw.drec_blocks;
-  wg_assign(p->wg, L.n_tiles, sm_count(), wa.part0);
+  wg_assign(p->wg, L.n_tiles, bwd_sms(), wa.part0);
 #ifdef NB_TIMING_EXPERIMENTS
   {
     static const int dbg = getenv("NB_WG_DEBUG") ? atoi(getenv("NB_WG_DEBUG")) : 0;

@@ -86,6 +86,10 @@ class TrainStep:
         # unable to shut down cleanly.
         self._split_graph = bool(int(os.environ.get("NB_SPLIT_GRAPH", "1")))
         self._overlap = bool(int(os.environ.get("NB_OVERLAP_ALLREDUCE", "1")))
+        # the backward kernels are persistent, one 215 KB CTA per SM: leave a few SMs to NCCL so that the fine network's
+        # all-reduce really runs under the coarse network's backward (NB_BWD_SM_RESERVE, default 8 when world > 1)
+        if self.world > 1 and self.mf is not None and self._overlap:
+            lib().nb_set_option(b"bwd_sm_reserve", int(os.environ.get("NB_BWD_SM_RESERVE", "8")))
         self.launches_per_step = None  # kernels inside one captured iteration (graph mode)
         self.graph_replays = 0
         if self.fused:
