@@ -16,7 +16,8 @@ OBJ = os.path.join(HERE, "build")
 LIB = os.path.join(HERE, "libnerf_b200.so")
 
 ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]
-COMMON = ["-O3", "-std=c++17", "-lineinfo", "-Xcompiler", "-fPIC"]
+# NB_EXTRA_NVCC_FLAGS=-DNB_TIMING_EXPERIMENTS builds the variant with the kernel-side timing hooks (tools/ only)
+COMMON = ["-O3", "-std=c++17", "-lineinfo", "-Xcompiler", "-fPIC"] + os.environ.get("NB_EXTRA_NVCC_FLAGS", "").split()
 # (source, extra flags).  The stage kernels must round like the reference's separate fp32 mul/add.
 SOURCES = [
     ("stages.cu", ["--fmad=false"]),

@@ -339,7 +339,7 @@ mlp_tc_kernel(const __grid_constant__ TcPlan plan, const unsigned char* __restri
       unsigned char* rec_t = rec ? rec + (size_t)(tile0 + t) * rec_stride : nullptr;
       mbar_wait(bar_enc_s, ph_enc);
       ph_enc ^= 1;
-      if (rec && elect_one()) {
+      if (rec && !NB_DBG(dbg & 4) && elect_one()) {
         bulk_s2g_hint(rec_t, act_s + enc_off, kBlockBytes, pol_rec);
         bulk_commit();
       }
@@ -357,7 +357,7 @@ mlp_tc_kernel(const __grid_constant__ TcPlan plan, const unsigned char* __restri
             mbar_wait(bar_encd_s, ph_encd);
             ph_encd ^= 1;
           }
-          if (rec && elect_one()) {
+          if (rec && !NB_DBG(dbg & 4) && elect_one()) {
             bulk_s2g_hint(rec_t + (size_t)e.w * kBlockBytes, act_s + (e.x & ~127u), kBlockBytes, pol_rec);
             bulk_commit();
           }
@@ -377,7 +377,7 @@ mlp_tc_kernel(const __grid_constant__ TcPlan plan, const unsigned char* __restri
           tc_mma(d_tmem, a_desc + 2, b_desc + 2, e.y, 1u);
           tc_commit(bar_empty_s + 8 * slot);  // (1 of 2 arrivals) frees the ring slot when these MMAs have read it
           if (fl & PF_LAST) {
-            if (rec) bulk_wait_read0();  // record stores have read the blocks this stage's epilogue overwrites
+            if (rec && !NB_DBG(dbg & 8)) bulk_wait_read0();  // record stores have read the blocks this stage's epilogue overwrites
             tc_commit(bar_acc_s);        // accumulator of this stage complete
           }
         }
@@ -460,7 +460,7 @@ mlp_tc_kernel(const __grid_constant__ TcPlan plan, const unsigned char* __restri
               mbar_arrive(smem_u32(bar_drain + t));
             }
             if (NB_DBG(dbg & 2)) { fence_async_smem(); mbar_arrive(smem_u32(bar_act + 4 * t + j)); continue; }
-            if (mrec != nullptr && relu) {
+            if (mrec != nullptr && relu && !NB_DBG(dbg & 16)) {
               // train: 1-bit ReLU mask of this row's 64 pre-activations for the dgrad chain (8 B per row instead of the
               // 128-byte activation row it used to re-read): element i of the block -> bit 31 - (i & 31) of word i >> 5,
               // set where the accumulator's sign bit is clear (funnel shifts collect the sign bits, one per value)
