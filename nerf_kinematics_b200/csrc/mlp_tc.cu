@@ -741,8 +741,13 @@ mlp_tc2_kernel(const __grid_constant__ TcPlan plan, const unsigned char* __restr
     unsigned char* enc_t = act_t + plan.n_act_blocks * kBlockBytes;
     float* apart = alpha_part + (t * 2 + par) * kTileM;
     // the issuers' barriers live in the leader CTA
+    // (the leader's own warps use the plain shared::cta window of the same barriers: mapa of rank 0 from rank 0 is
+    // the same object, but the shared::cluster form goes through the cluster path)
     const uint32_t l_enc = mapa_u32(smem_u32(bar_enc + t), 0), l_encd = mapa_u32(smem_u32(bar_encd + t), 0);
     const uint32_t l_act = mapa_u32(smem_u32(bar_act + 4 * t), 0), l_drain = mapa_u32(smem_u32(bar_drain + t), 0);
+    const uint32_t c_enc = smem_u32(bar_enc + t), c_encd = smem_u32(bar_encd + t);
+    const uint32_t c_act = smem_u32(bar_act + 4 * t), c_drain = smem_u32(bar_drain + t);
+#define NB_ARRIVE2(local, remote) do { if (leader) mbar_arrive(local); else mbar_arrive_cluster(remote); } while (0)
     uint32_t acc_phase = 0;
     for (long long rd = 0; rd < n_rounds; ++rd) {
       const long long stream_tile0 = tile_begin + 4 * rd + 2 * t;
@@ -775,7 +780,7 @@ mlp_tc2_kernel(const __grid_constant__ TcPlan plan, const unsigned char* __restr
       }
       fence_async_smem();
       __syncwarp();
-      if (lane == 0) mbar_arrive_cluster(l_enc);
+      if (lane == 0) NB_ARRIVE2(c_enc, l_enc);
 
       for (int s = 0; s < plan.n_stages; ++s) {
         const TcStage& st = plan.st[s];
@@ -790,7 +795,7 @@ mlp_tc2_kernel(const __grid_constant__ TcPlan plan, const unsigned char* __restr
           if (par >= nblk) {
             tc_fence_before();
             __syncwarp();
-            if (lane == 0) mbar_arrive_cluster(l_drain);
+            if (lane == 0) NB_ARRIVE2(c_drain, l_drain);
           }
           for (int j = par; j < nblk; j += 2) {
             uint32_t v[64];
@@ -803,7 +808,7 @@ mlp_tc2_kernel(const __grid_constant__ TcPlan plan, const unsigned char* __restr
             if (j + 2 >= nblk) {
               tc_fence_before();
               __syncwarp();
-              if (lane == 0) mbar_arrive_cluster(l_drain);
+              if (lane == 0) NB_ARRIVE2(c_drain, l_drain);
             }
             const uint32_t rp = smem_u32(act_t) + j * kBlockBytes + row * 128;
             if (st.alpha_dot) {
@@ -819,14 +824,14 @@ mlp_tc2_kernel(const __grid_constant__ TcPlan plan, const unsigned char* __restr
             }
             fence_async_smem();
             __syncwarp();
-            if (lane == 0) mbar_arrive_cluster(l_act + 8 * j);
+            if (lane == 0) NB_ARRIVE2(c_act + 8 * j, l_act + 8 * j);
           }
           if (st.alpha_dot) apart[row] = adot;
           if (st.write_encd && par == 1) {
             encode_row<0, 8>(enc_t, row, v0, v1, v2, plan.Ld);
             fence_async_smem();
             __syncwarp();
-            if (lane == 0) mbar_arrive_cluster(l_encd);
+            if (lane == 0) NB_ARRIVE2(c_encd, l_encd);
           }
         } else {
           uint32_t v[4] = {0u, 0u, 0u, 0u};
@@ -836,7 +841,7 @@ mlp_tc2_kernel(const __grid_constant__ TcPlan plan, const unsigned char* __restr
           }
           tc_fence_before();
           __syncwarp();
-          if (lane == 0) mbar_arrive_cluster(l_drain);
+          if (lane == 0) NB_ARRIVE2(c_drain, l_drain);
           if (par == 0) {
             float4 o;
             o.x = __uint_as_float(v[0]) * kInvActScale + bs[0];
@@ -854,6 +859,7 @@ mlp_tc2_kernel(const __grid_constant__ TcPlan plan, const unsigned char* __restr
       }
     }
   }
+#undef NB_ARRIVE2
   // ---- teardown: nobody leaves (or frees tensor memory) while the other CTA may still signal or be signalled
   tc_fence_before();
   __syncthreads();

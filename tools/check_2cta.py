@@ -35,11 +35,12 @@ for name, m in models.items():
         d = torch.nn.functional.normalize(torch.randn(n, 3, device=dev), dim=-1)
         rays = ops.make_ray_batch(o, d, 2.0, 6.0, use_viewdirs=bool(m.use_viewdirs))
         z = ops.sample_coarse(rays, S)
-        a, b = fwd(m, rays, z, 0), fwd(m, rays, z, 1)
+        a, b, b2 = fwd(m, rays, z, 0), fwd(m, rays, z, 1), fwd(m, rays, z, 1)
         same = torch.equal(a, b)
         ok &= same
-        print("%-13s rays %5d x %3d (%5d tiles): %s  max|diff| %.3e" % (name, n, S, (n * S + 127) // 128, "equal" if same else "DIFFERENT",
-                                                                      float((a - b).abs().max())), flush=True)
+        print("%-13s rays %5d x %3d (%5d tiles): %s  max|diff| %.3e  | 2cta run-to-run %s  frac differing %.4f" % (
+            name, n, S, (n * S + 127) // 128, "equal" if same else "DIFFERENT", float((a - b).abs().max()),
+            "deterministic" if torch.equal(b, b2) else "VARIES", float((a != b).float().mean())), flush=True)
 m = models["8x256"]
 n, S = 32768, 192
 o = torch.randn(n, 3, device=dev) * 0.5 + torch.tensor([0, 0, 4.0], device=dev)
