@@ -41,6 +41,9 @@ for name, m in models.items():
         print("%-13s rays %5d x %3d (%5d tiles): %s  max|diff| %.3e  | 2cta run-to-run %s  frac differing %.4f" % (
             name, n, S, (n * S + 127) // 128, "equal" if same else "DIFFERENT", float((a - b).abs().max()),
             "deterministic" if torch.equal(b, b2) else "VARIES", float((a != b).float().mean())), flush=True)
+        if not same and n * S <= 2048:
+            rows = torch.nonzero((a != b).reshape(-1, 4).any(-1)).flatten()
+            print("      differing points (index, index %% 128):", [(int(r), int(r) % 128) for r in rows[:24]], flush=True)
 m = models["8x256"]
 n, S = 32768, 192
 o = torch.randn(n, 3, device=dev) * 0.5 + torch.tensor([0, 0, 4.0], device=dev)
