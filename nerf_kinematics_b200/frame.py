@@ -50,7 +50,11 @@ class FrameRenderer:
         f = lambda *s: torch.empty(s, dtype=torch.float32, device=dev)
         n = max(self.n, 1)
         self.pose_dev = torch.zeros(12, dtype=torch.float32, device=dev)
-        self.pose_pin = torch.zeros(12, dtype=torch.float32).pin_memory()
+        # host -> device pose staging: a ring of pinned slots, each guarded by an event, so that the host running ahead of
+        # the GPU (frames are GPU-bound) never overwrites a pose whose asynchronous copy has not executed yet
+        self._pose_ring = torch.zeros(8, 12, dtype=torch.float32).pin_memory()
+        self._pose_ev = [None] * 8
+        self._pose_i = 0
         self.ro, self.rd, self.packed = f(n, 3), f(n, 3), f(n, self.stride)
         keys = ["rgb", "disp", "acc"] + (["rgb0", "disp0", "acc0", "z_std"] if self.I > 0 else [])
         self.out = {k: (f(n, 3) if _WIDTH[k] == 3 else f(n)) for k in keys}
@@ -118,8 +122,15 @@ class FrameRenderer:
             elif isinstance(c2w, torch.Tensor) and c2w.is_cuda:
                 self.pose_dev.copy_(c2w[:3, :4].to(torch.float32).reshape(-1))
             else:
-                self.pose_pin.copy_(torch.as_tensor(np.asarray(c2w, dtype=np.float32))[:3, :4].reshape(-1))
-                self.pose_dev.copy_(self.pose_pin, non_blocking=True)
+                i = self._pose_i
+                self._pose_i = (i + 1) % self._pose_ring.shape[0]
+                if self._pose_ev[i] is not None:
+                    self._pose_ev[i].synchronize()
+                self._pose_ring[i].copy_(torch.as_tensor(np.asarray(c2w, dtype=np.float32))[:3, :4].reshape(-1))
+                self.pose_dev.copy_(self._pose_ring[i], non_blocking=True)
+                if self._pose_ev[i] is None:
+                    self._pose_ev[i] = torch.cuda.Event()
+                self._pose_ev[i].record()
             hc, hf = self._handles()   # repacks the 16-bit images only when the parameters changed (eager, outside the graph)
             if self.check_numerics:
                 self.flag.zero_()

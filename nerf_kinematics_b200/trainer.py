@@ -99,7 +99,11 @@ class TrainStep:
             self._segments = [(self.mc, 0, nc)] + ([(self.mf, off_f, nf)] if nf else [])
             self._step_t = torch.zeros((), dtype=torch.float32)  # torch keeps `step` as a CPU fp32 scalar tensor
             self._alias_optimizer_state()
-            self.hyper_host = torch.zeros((8,), dtype=torch.float32).pin_memory() if dev.type == "cuda" else None
+            # pinned staging ring for the per-step hyper-parameters (the host runs ahead of the GPU: a single slot could
+            # be overwritten before its asynchronous copy has executed)
+            self.hyper_host = torch.zeros((16, 8), dtype=torch.float32).pin_memory() if dev.type == "cuda" else None
+            self._hyper_ev = [None] * 16
+            self._hyper_i = 0
             self.hyper = torch.zeros((8,), dtype=torch.float32, device=dev)
 
     # ------------------------------------------------------------------ optimizer state (checkpoint layout)
@@ -262,9 +266,17 @@ class TrainStep:
         b1, b2 = self.betas
         vals = [self.learning_rate(self.global_step), b1, b2, self.eps, 1.0 - b1 ** t, 1.0 - b2 ** t, 1.0 - b1, 1.0 - b2]
         if self.hyper_host is not None:
+            k = self._hyper_i
+            self._hyper_i = (k + 1) % self.hyper_host.shape[0]
+            if self._hyper_ev[k] is not None:
+                self._hyper_ev[k].synchronize()
+            slot = self.hyper_host[k]
             for i, v in enumerate(vals):
-                self.hyper_host[i] = v
-            self.hyper.copy_(self.hyper_host, non_blocking=True)
+                slot[i] = v
+            self.hyper.copy_(slot, non_blocking=True)
+            if self._hyper_ev[k] is None:
+                self._hyper_ev[k] = torch.cuda.Event()
+            self._hyper_ev[k].record()
         else:
             self.hyper.copy_(torch.tensor(vals, dtype=torch.float32))
 
