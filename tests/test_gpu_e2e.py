@@ -301,3 +301,21 @@ def test_full_size_lego_frame_properties_and_row_block_sharding():
         sel = torch.stack([ro[r0:r1].reshape(-1, 3), rd[r0:r1].reshape(-1, 3)])
         r2, _, a2, _ = nk.render(H, W, focal, chunk=7000, rays=sel, use_viewdirs=True, ndc=False, near=2.0, far=6.0, **kw)
         assert torch.equal(r2.reshape(r1 - r0, W, 3), rgb[r0:r1]) and torch.equal(a2.reshape(r1 - r0, W), acc[r0:r1])
+
+
+def test_render_path_many_poses_each_frame_is_its_own_pose():
+    """render_path replays one captured frame graph per pose while the host runs ahead of the GPU: every frame must be
+    rendered with ITS pose (the pose travels through a ring of pinned staging slots), also when the same renderer is
+    then asked for single frames."""
+    g = load_golden("e2e_lego")
+    mc, mf = _models("ckpt_lego_lowres3")
+    kw = dict(network_query_fn=None, perturb=0.0, N_importance=128, network_fine=mf, N_samples=64, network_fn=mc,
+              use_viewdirs=True, white_bkgd=True, raw_noise_std=0.0, ndc=False, lindisp=False, near=2.0, far=6.0)
+    H = W = 96
+    poses = [O.pose_spherical(-180.0 + 17.0 * i, -30.0, 4.0).numpy() for i in range(20)]
+    with torch.no_grad():
+        rgbs, disps = nk.render_path(poses, (H, W, 130.0), 4096, kw)
+        for i in (0, 7, 13, 19):
+            one = nk.render(H, W, 130.0, chunk=4096, c2w=poses[i][:3, :4], **kw)[0]
+            assert np.array_equal(rgbs[i], one.cpu().numpy()), i
+    assert rgbs.shape == (20, H, W, 3) and float(np.abs(rgbs[0] - rgbs[1]).max()) > 1e-3
