@@ -154,8 +154,9 @@ def render_path(render_poses, hwf, chunk, render_kwargs, gt_imgs=None, savedir=N
         H, W = H // render_factor, W // render_factor
         focal = focal / render_factor if not hasattr(focal, "shape") or np.ndim(focal) == 0 else _scale_K(focal, render_factor)
     # the reference converts every frame with .numpy() as soon as it is rendered (run_nerf.py:358),
-    # which serialises host and device.  Here each frame is copied into pinned host memory asynchronously (the next
-    # pose renders while the previous one drains), to8b / PSNR run on the device, and the host waits once at the end.
+    # which serialises host and device.  Here each frame is copied into a pinned ring slot asynchronously (the next
+    # poses render while it drains; _FrameDrain), to8b / PSNR run on the device, the host only ever waits for a frame
+    # that is R = 4 frames old.
     rows = None
     if row_block is not None:
         rank, world = row_block
@@ -164,7 +165,8 @@ def render_path(render_poses, hwf, chunk, render_kwargs, gt_imgs=None, savedir=N
         rows = (r0, r0 + base + (1 if rank < rem else 0))
     poses_list = [(c if isinstance(c, torch.Tensor) else torch.as_tensor(np.asarray(c)))[:3, :4] for c in render_poses]
     M = len(poses_list)
-    rgbs_h = disps_h = u8_h = None
+    rgbs = disps = None          # the results: ordinary numpy arrays, like the reference's np.stack(rgbs, 0)
+    ring = None                  # _FrameDrain: a few pinned frame slots the device copies into asynchronously
     psnrs = []
     t = time.time()
     with torch.no_grad():
@@ -176,34 +178,82 @@ def render_path(render_poses, hwf, chunk, render_kwargs, gt_imgs=None, savedir=N
             # same stream overwrites them -- no per-frame clone
             rgb, disp, acc, _ = render(H, W, focal, chunk=chunk, c2w=c2w, _static_outputs=True, _rows=rows,
                                        **render_kwargs)
-            if rgbs_h is None:
-                pin = rgb.is_cuda
-                rgbs_h = torch.empty((M,) + tuple(rgb.shape), dtype=torch.float32, pin_memory=pin)
-                disps_h = torch.empty((M,) + tuple(disp.shape), dtype=torch.float32, pin_memory=pin)
-                if savedir is not None:
-                    u8_h = torch.empty((M,) + tuple(rgb.shape), dtype=torch.uint8, pin_memory=pin)
-            rgbs_h[i].copy_(rgb, non_blocking=True)
-            disps_h[i].copy_(disp, non_blocking=True)
+            if rgbs is None:
+                rgbs = np.empty((M,) + tuple(rgb.shape), np.float32)
+                disps = np.empty((M,) + tuple(disp.shape), np.float32)
+                ring = _FrameDrain(tuple(rgb.shape), tuple(disp.shape), savedir is not None, rgb.is_cuda)
+            u8 = None
             want_psnr = gt_imgs is not None and render_factor == 0 and verbose
             if want_psnr or savedir is not None:
                 gt = torch.as_tensor(np.asarray(gt_imgs[i]), dtype=torch.float32) if want_psnr else None
                 if gt is not None and rows is not None:
                     gt = gt[rows[0]:rows[1]]
                 u8, psnr = ops.to8b_psnr(rgb, gt, want_u8=savedir is not None)
-                if u8 is not None:
-                    u8_h[i].copy_(u8, non_blocking=True)
                 if psnr is not None:
                     psnrs.append(psnr)
-    if rgbs_h is None:
+            ring.push(i, rgb, disp, u8, rgbs, disps, savedir)
+    if rgbs is None:
         return np.zeros((0, H, W, 3), np.float32), np.zeros((0, H, W), np.float32)
-    if torch.cuda.is_available():
-        torch.cuda.synchronize()
+    ring.finish(rgbs, disps, savedir)
     for p in psnrs:
         print(float(p))
-    if savedir is not None:
-        for i in range(M):
-            _write_png(os.path.join(savedir, "{:03d}.png".format(i)), u8_h[i].numpy())
-    return rgbs_h.numpy(), disps_h.numpy()
+    return rgbs, disps
+
+
+_DRAIN_CACHE = {}
+
+
+class _FrameDrain:
+    """Frames leave the device through a ring of pinned slots (allocated once per frame shape: pinning M whole frames per
+    call costs more than rendering them at small sizes).  Frame i is copied device -> slot i % R asynchronously; when the
+    slot comes round again -- R frames later, so the host never waits for the frame being rendered -- its event is
+    awaited and the frame is moved into the caller's numpy arrays (and written as a PNG when asked)."""
+    R = 4
+
+    def __init__(self, rgb_shape, disp_shape, want_u8, cuda):
+        key = (rgb_shape, disp_shape, bool(want_u8), bool(cuda))
+        ent = _DRAIN_CACHE.get(key)
+        if ent is None:
+            if len(_DRAIN_CACHE) >= 4:
+                _DRAIN_CACHE.clear()
+            ent = {"rgb": torch.empty((self.R,) + rgb_shape, dtype=torch.float32, pin_memory=cuda),
+                   "disp": torch.empty((self.R,) + disp_shape, dtype=torch.float32, pin_memory=cuda),
+                   "u8": torch.empty((self.R,) + rgb_shape, dtype=torch.uint8, pin_memory=cuda) if want_u8 else None}
+            _DRAIN_CACHE[key] = ent
+        self.buf = ent
+        self.ev = [None] * self.R
+        self.frame = [None] * self.R
+        self.cuda = cuda
+
+    def _retire(self, s, rgbs, disps, savedir):
+        i = self.frame[s]
+        if i is None:
+            return
+        if self.ev[s] is not None:
+            self.ev[s].synchronize()
+        rgbs[i] = self.buf["rgb"][s].numpy()
+        disps[i] = self.buf["disp"][s].numpy()
+        if savedir is not None and self.buf["u8"] is not None:
+            _write_png(os.path.join(savedir, "{:03d}.png".format(i)), self.buf["u8"][s].numpy())
+        self.frame[s] = None
+
+    def push(self, i, rgb, disp, u8, rgbs, disps, savedir):
+        s = i % self.R
+        self._retire(s, rgbs, disps, savedir)
+        self.buf["rgb"][s].copy_(rgb, non_blocking=True)
+        self.buf["disp"][s].copy_(disp, non_blocking=True)
+        if u8 is not None:
+            self.buf["u8"][s].copy_(u8, non_blocking=True)
+        if self.cuda:
+            if self.ev[s] is None:
+                self.ev[s] = torch.cuda.Event()
+            self.ev[s].record()
+        self.frame[s] = i
+
+    def finish(self, rgbs, disps, savedir):
+        order = sorted((f, s) for s, f in enumerate(self.frame) if f is not None)
+        for _, s in order:
+            self._retire(s, rgbs, disps, savedir)
 
 
 def _scale_K(K, factor):
