@@ -52,32 +52,55 @@ __device__ __forceinline__ void pixel_ray(int col, int row, float fx, float fy, 
   for (int k = 0; k < 3; ++k) d[k] = (dx * cam.r[4 * k + 0] + dy * cam.r[4 * k + 1]) + dz * cam.r[4 * k + 2];
 }
 
-// grid = (ceil(W / 256), rows): a block owns up to 256 consecutive pixels of one row, stages their 768 floats in shared
-// memory and writes them back as fully coalesced 128-byte warp stores (no 64-bit index division, no strided stores).
+// grid = (ceil(W / 256), ceil(rows / kRaysRows)): a block owns up to 256 consecutive pixels of kRaysRows rows; per row it
+// stages the 768 direction floats in shared memory and writes them back as coalesced 16-byte stores (scalar stores when
+// the row segment is not 16-byte aligned: W * 3 not a multiple of 4); the origins are the same 12 bytes for every ray.
+constexpr int kRaysRows = 8;
 __global__ void __launch_bounds__(256)
 get_rays_kernel(int W, float fx, float fy, float cx, float cy, Cam cam, const float* __restrict__ cam_dev, int row0,
-                float* __restrict__ ro, float* __restrict__ rd) {
-  __shared__ float sd[768];
+                int n_rows, float* __restrict__ ro, float* __restrict__ rd) {
+  __shared__ __align__(16) float sd[768];
   if (cam_dev != nullptr) {  // pose in device memory (a captured frame graph reads the pose of the replay, not of the capture)
 #pragma unroll
     for (int k = 0; k < 12; ++k) cam.r[k] = __ldg(cam_dev + k);
   }
   const int col0 = blockIdx.x * 256, col = col0 + threadIdx.x;
-  const int row = row0 + blockIdx.y;
   const int npix = min(256, W - col0);
-  if (col < W) {
-    float d[3];
-    pixel_ray(col, row, fx, fy, cx, cy, cam, d);
-    sd[3 * threadIdx.x + 0] = d[0];
-    sd[3 * threadIdx.x + 1] = d[1];
-    sd[3 * threadIdx.x + 2] = d[2];
+  const int nflt = 3 * npix;
+  // origin pattern of this thread's float4 slot: element i of a row segment holds cam.r[4 * (i % 3) + 3]
+  float4 o4;
+  {
+    const int i0 = (4 * threadIdx.x) % 3;
+    o4.x = cam.r[4 * i0 + 3];
+    o4.y = cam.r[4 * ((i0 + 1) % 3) + 3];
+    o4.z = cam.r[4 * ((i0 + 2) % 3) + 3];
+    o4.w = cam.r[4 * i0 + 3];
   }
-  __syncthreads();
-  const int64_t base = ((int64_t)blockIdx.y * W + col0) * 3;
-  for (int i = threadIdx.x; i < 3 * npix; i += 256) {
-    rd[base + i] = sd[i];
-    const int k = i % 3;
-    ro[base + i] = cam.r[4 * k + 3];
+  const int r_begin = blockIdx.y * kRaysRows, r_end = min(n_rows, r_begin + kRaysRows);
+  for (int r = r_begin; r < r_end; ++r) {
+    if (col < W) {
+      float d[3];
+      pixel_ray(col, row0 + r, fx, fy, cx, cy, cam, d);
+      sd[3 * threadIdx.x + 0] = d[0];
+      sd[3 * threadIdx.x + 1] = d[1];
+      sd[3 * threadIdx.x + 2] = d[2];
+    }
+    __syncthreads();
+    const int64_t base = ((int64_t)r * W + col0) * 3;
+    if ((base & 3) == 0 && (nflt & 3) == 0) {
+      float4* rd4 = reinterpret_cast<float4*>(rd + base);
+      float4* ro4 = reinterpret_cast<float4*>(ro + base);
+      if ((int)threadIdx.x < (nflt >> 2)) {
+        rd4[threadIdx.x] = reinterpret_cast<const float4*>(sd)[threadIdx.x];
+        ro4[threadIdx.x] = o4;
+      }
+    } else {
+      for (int i = threadIdx.x; i < nflt; i += 256) {
+        rd[base + i] = sd[i];
+        ro[base + i] = cam.r[4 * (i % 3) + 3];
+      }
+    }
+    __syncthreads();
   }
 }
 
@@ -298,9 +321,9 @@ static int get_rays_common(int H, int W, float fx, float fy, float cx, float cy,
   NB_REQUIRE(rays_o && rays_d, "nb_get_rays: null output");
   Cam cam{};
   if (c2w_host) memcpy(cam.r, c2w_host, sizeof(cam.r));
-  NB_REQUIRE(row1 - row0 <= 65535, "nb_get_rays: more than 65535 rows in one call");
-  dim3 grid((unsigned)ceil_div(W, 256), (unsigned)(row1 - row0));
-  get_rays_kernel<<<grid, 256, 0, as_stream(stream)>>>(W, fx, fy, cx, cy, cam, c2w_dev, row0, rays_o, rays_d);
+  NB_REQUIRE(row1 - row0 <= 65535 * kRaysRows, "nb_get_rays: too many rows in one call");
+  dim3 grid((unsigned)ceil_div(W, 256), (unsigned)ceil_div(row1 - row0, kRaysRows));
+  get_rays_kernel<<<grid, 256, 0, as_stream(stream)>>>(W, fx, fy, cx, cy, cam, c2w_dev, row0, row1 - row0, rays_o, rays_d);
   NB_LAUNCHED();
   return NB_OK;
 }
