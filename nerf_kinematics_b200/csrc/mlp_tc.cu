@@ -132,8 +132,10 @@ __device__ __forceinline__ void encode_row(unsigned char* block, int row, float 
     for (int k = 0; k < 3; ++k) {
       ch[3 + 6 * f + k] = on ? s[k] : 0.0f;
       ch[6 + 6 * f + k] = on ? c[k] : 0.0f;
-      const float s2 = 2.0f * s[k] * c[k];
-      const float c2 = 1.0f - 2.0f * s[k] * s[k];
+      // explicit roundings: left to the compiler, the contraction into FMAs differs between instantiations (kernels), and a
+      // last-bit difference at octave 0 is 2^9 ulp at octave 9 -- enough to flip fp16 roundings in ~10 % of the points
+      const float s2 = __fmul_rn(__fmul_rn(2.0f, s[k]), c[k]);
+      const float c2 = __fmaf_rn(__fmul_rn(-2.0f, s[k]), s[k], 1.0f);
       s[k] = s2; c[k] = c2;
     }
   }
@@ -524,6 +526,287 @@ mlp_tc_kernel(const __grid_constant__ TcPlan plan, const unsigned char* __restri
     }
   }
   // ---- teardown
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    __syncwarp();
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(512));
+  }
+}
+
+// ------------------------------------------------------------------------------------ four-tile kernel for narrow graphs
+// Inference kernel for graphs whose stages are all N <= 128 (FlexibleNeRFModel 4x128: every checkpoint the reference
+// ships).  A 128-wide layer is 9 MMAs of ~80 cycles against the same per-stage hand-off chain as a 256-wide one
+// (commit -> epilogue wakes -> tcgen05.ld -> convert -> publish -> next MMA, ~2 000 cycles), so two tiles in flight leave
+// the tensor pipe idle most of the time (0.24 of peak).  Narrow tiles are cheap, though: 3 operand blocks (48 KB) and 128
+// TMEM columns each, so FOUR fit in one CTA.  Same roles and step program as mlp_tc_kernel with
+//   warp 0        weight producer (ring of 8 KB slots: <= 128 rows x 32 K-elements)
+//   warps 1-4     MMA issuers, one per tile slot
+//   warps 5-20    epilogue, four warps per tile (one per TMEM lane quarter, thread == row, all column blocks)
+constexpr int kThreadsTc4 = 672;
+constexpr int kRing4 = 3;
+constexpr int kSlot4Bytes = 128 * 64;
+
+__global__ void __launch_bounds__(kThreadsTc4, 1)
+mlp_tc4_kernel(const __grid_constant__ TcPlan plan, const unsigned char* __restrict__ wpk, const float* __restrict__ bias_g,
+               TcSrc src, long long n_points, float* __restrict__ raw) {
+  extern __shared__ __align__(1024) unsigned char smem_raw[];
+  unsigned char* smem = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  const int tile_blocks = plan.n_act_blocks + 1;
+  const int tile_bytes = tile_blocks * kBlockBytes;
+  unsigned char* act = smem;                                 // [4 tiles][tile_blocks][16 KB]
+  unsigned char* ring = act + 4 * tile_bytes;                // [kRing4][8 KB]
+  float* bias_s = reinterpret_cast<float*>(ring + kRing4 * kSlot4Bytes);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(bias_s + ((plan.n_bias + 3) & ~3));
+  uint64_t* bar_full = bars;                    // [kRing4]
+  uint64_t* bar_empty = bar_full + kRing4;      // [kRing4]  four commits (one per issuer) free a slot
+  uint64_t* bar_enc = bar_empty + kRing4;       // [4]  position encoding of tile t written (128 arrivals)
+  uint64_t* bar_encd = bar_enc + 4;             // [4]  direction encoding (128)
+  uint64_t* bar_act = bar_encd + 4;             // [4][2] activation block j of tile t written (128)
+  uint64_t* bar_drain = bar_act + 8;            // [4]  accumulator of tile t read out (128)
+  uint64_t* bar_acc = bar_drain + 4;            // [4]  accumulator of tile t's current stage complete
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bar_acc + 4);
+  uint4* prog = reinterpret_cast<uint4*>(tmem_slot + 4);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const long long n_tiles = (n_points + kTileM - 1) / kTileM;
+  const long long tile_begin = n_tiles * blockIdx.x / gridDim.x;
+  const long long tile_end = n_tiles * (blockIdx.x + 1) / gridDim.x;
+  const long long n_rounds = (tile_end - tile_begin + 3) >> 2;
+
+  if (threadIdx.x == 0) {
+    for (int i = 0; i < kRing4; ++i) {
+      mbar_init(smem_u32(bar_full + i), 1);
+      mbar_init(smem_u32(bar_empty + i), 4);
+    }
+    for (int t = 0; t < 4; ++t) {
+      mbar_init(smem_u32(bar_acc + t), 1);
+      mbar_init(smem_u32(bar_enc + t), 128);
+      mbar_init(smem_u32(bar_encd + t), 128);
+      mbar_init(smem_u32(bar_act + 2 * t), 128);
+      mbar_init(smem_u32(bar_act + 2 * t + 1), 128);
+      mbar_init(smem_u32(bar_drain + t), 128);
+    }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (threadIdx.x == 32) {
+    // step program (see mlp_tc_kernel): x = A operand offset inside a tile's region, y = instruction descriptor, z = flags
+    int i = 0;
+    bool encd_pending = false;
+    for (int s = 0; s < plan.n_stages; ++s) {
+      const TcStage& st = plan.st[s];
+      for (int kb = 0; kb < st.n_kb; ++kb) {
+        const int sidx = st.a_src[kb];
+        for (int h = sidx == SRC_BIAS ? 1 : 0; h < 2; ++h) {
+          uint4 e;
+          e.x = (uint32_t)((sidx < 4 ? sidx : plan.n_act_blocks) * kBlockBytes + h * 64);
+          e.y = umma_idesc(st.n_main);
+          e.z = sidx == SRC_BIAS ? PF_BIAS : 0u;
+          e.w = 0u;
+          if (h == 0 && sidx < 4) e.z |= PF_WAIT_ACT | (uint32_t)sidx;
+          if ((sidx == SRC_ENCD || sidx == SRC_BIAS) && encd_pending) { e.z |= PF_WAIT_ENCD; encd_pending = false; }
+          if (kb == 0 && h == 0) e.z |= PF_FIRST;
+          if (kb == st.n_kb - 1 && h == 1) e.z |= PF_LAST;
+          if ((kb | h) != 0) e.z |= PF_ACC;
+          prog[i++] = e;
+        }
+      }
+      if (st.write_encd) encd_pending = true;
+    }
+  }
+  if (warp == 1) {  // TMEM: all 512 columns; tile slot t owns columns [128 t, 128 t + 128)
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "r"(512));
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
+  }
+  for (int i = threadIdx.x; i < plan.n_bias; i += blockDim.x) bias_s[i] = bias_g[i];
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+  const int n_steps = plan.n_steps;
+
+  if (warp == 0) {
+    // ============================ weight producer ============================
+    if (lane == 0) {
+      uint32_t slot = 0, phase = 0;
+      const uint64_t pol_w = l2_evict_last();
+      for (long long rd = 0; rd < n_rounds; ++rd) {
+        for (int s = 0; s < plan.n_stages; ++s) {
+          const TcStage& st = plan.st[s];
+          for (int kb = 0; kb < st.n_kb; ++kb) {
+            for (int h = st.a_src[kb] == SRC_BIAS ? 1 : 0; h < 2; ++h) {
+              const uint32_t bytes = (uint32_t)st.n_main * 64u;
+              mbar_wait(smem_u32(bar_empty + slot), phase ^ 1);
+              const uint32_t fb = smem_u32(bar_full + slot);
+              mbar_expect_tx(fb, bytes);
+              bulk_g2s_hint(smem_u32(ring + slot * kSlot4Bytes),
+                            wpk + st.w_off + (size_t)kb * st.chunk_bytes + (size_t)h * bytes, bytes, fb, pol_w);
+              if (++slot == kRing4) { slot = 0; phase ^= 1; }
+            }
+          }
+        }
+      }
+    }
+  } else if (warp <= 4) {
+    // ============================ MMA issuers (one warp per tile slot) ============================
+    const int t = warp - 1;
+    uint32_t slot = 0, phase = 0;
+    uint32_t ph_act = 0, ph_enc = 0, ph_encd = 0, ph_drain = 0;
+    bool armed = false;
+    const uint32_t act_s = smem_u32(act) + t * tile_bytes, ring_s = smem_u32(ring);
+    const uint32_t bar_full_s = smem_u32(bar_full), bar_empty_s = smem_u32(bar_empty), bar_act_s = smem_u32(bar_act + 2 * t);
+    const uint32_t bar_enc_s = smem_u32(bar_enc + t), bar_encd_s = smem_u32(bar_encd + t);
+    const uint32_t bar_drain_s = smem_u32(bar_drain + t), bar_acc_s = smem_u32(bar_acc + t);
+    const uint32_t d_tmem = tmem_base + t * 128;
+    for (long long rd = 0; rd < n_rounds; ++rd) {
+      if (tile_begin + 4 * rd + t >= tile_end) {
+        // unpopulated slot of the last round: only keep the ring's four-commit protocol going
+        for (int i = 0; i < n_steps; ++i) {
+          mbar_wait(bar_full_s + 8 * slot, phase);
+          if (elect_one()) tc_commit(bar_empty_s + 8 * slot);
+          __syncwarp();
+          if (++slot == kRing4) { slot = 0; phase ^= 1; }
+        }
+        continue;
+      }
+      mbar_wait(bar_enc_s, ph_enc);
+      ph_enc ^= 1;
+      uint4 e = prog[0];
+      for (int i = 0; i < n_steps; ++i) {
+        const uint4 en = prog[i + 1 < n_steps ? i + 1 : i];
+        const uint32_t fl = e.z;
+        if (fl & PF_WAIT_ACT) {
+          const uint32_t j = fl & 3u;
+          mbar_wait(bar_act_s + 8 * j, (ph_act >> j) & 1u);
+          ph_act ^= 1u << j;
+        } else if (fl & PF_WAIT_ENCD) {
+          mbar_wait(bar_encd_s, ph_encd);
+          ph_encd ^= 1;
+        }
+        if ((fl & PF_FIRST) && armed) {
+          mbar_wait(bar_drain_s, ph_drain);
+          ph_drain ^= 1;
+        }
+        armed = true;
+        mbar_wait(bar_full_s + 8 * slot, phase);
+        tc_fence_after();
+        const uint64_t a_desc = kDescHiSw128 | (uint64_t)(((act_s + e.x) & 0x3FFFFu) >> 4);
+        const uint64_t b_desc = kDescHiSw64 | (uint64_t)(((ring_s + slot * kSlot4Bytes) & 0x3FFFFu) >> 4);
+        if (elect_one()) {
+          if (!(fl & PF_BIAS)) tc_mma(d_tmem, a_desc, b_desc, e.y, (fl & PF_ACC) ? 1u : 0u);
+          tc_mma(d_tmem, a_desc + 2, b_desc + 2, e.y, 1u);
+          tc_commit(bar_empty_s + 8 * slot);
+          if (fl & PF_LAST) tc_commit(bar_acc_s);
+        }
+        __syncwarp();
+        if (++slot == kRing4) { slot = 0; phase ^= 1; }
+        e = en;
+      }
+    }
+  } else {
+    // ============================ epilogue warps (thread == row), four per tile ============================
+    const int ew = warp - 5;
+    const int t = ew >> 2;
+    const int q = warp & 3;             // TMEM lane quarter this warp may access
+    const int row = q * 32 + lane;
+    const int sw = row & 7;
+    const uint32_t t_main = tmem_base + (((uint32_t)(q * 32)) << 16) + t * 128;
+    unsigned char* act_t = act + t * tile_bytes;
+    unsigned char* enc_t = act_t + plan.n_act_blocks * kBlockBytes;
+    uint32_t acc_phase = 0;
+    for (long long rd = 0; rd < n_rounds; ++rd) {
+      const long long tile = tile_begin + 4 * rd + t;
+      if (tile >= tile_end) break;
+      long long p = tile * kTileM + row;
+      const bool in_range = p < n_points;
+      if (!in_range) p = n_points - 1;
+      float v0 = 0.f, v1 = 0.f, v2 = 0.f;
+      {
+        float x0, x1, x2;
+        if (src.rays != nullptr) {
+          const long long r = p / src.S;
+          const float* ry = src.rays + r * src.stride;
+          const float zz = src.z[p];
+          x0 = __fadd_rn(ry[0], __fmul_rn(ry[3], zz));
+          x1 = __fadd_rn(ry[1], __fmul_rn(ry[4], zz));
+          x2 = __fadd_rn(ry[2], __fmul_rn(ry[5], zz));
+          if (plan.Cd > 0) { v0 = ry[8]; v1 = ry[9]; v2 = ry[10]; }
+        } else {
+          x0 = src.pts[3 * p]; x1 = src.pts[3 * p + 1]; x2 = src.pts[3 * p + 2];
+          if (plan.Cd > 0) {
+            const float* vv = src.viewdirs + (p / src.per_dir) * 3;
+            v0 = vv[0]; v1 = vv[1]; v2 = vv[2];
+          }
+        }
+        encode_row<0, 8>(enc_t, row, x0, x1, x2, plan.Lx);
+      }
+      fence_async_smem();
+      mbar_arrive(smem_u32(bar_enc + t));
+
+      float alpha_dot = 0.0f;   // <last trunk activation row, alpha weights>, formed where that layer is converted
+      for (int s = 0; s < plan.n_stages; ++s) {
+        const TcStage& st = plan.st[s];
+        mbar_wait(smem_u32(bar_acc + t), acc_phase);
+        acc_phase ^= 1;
+        tc_fence_after();
+        const float* bs = bias_s + st.b_off;
+        if (st.epi == EPI_HIDDEN) {
+          const bool relu = st.relu != 0;
+          const int nblk = st.n_act >> 6;
+          // <activation, alpha weights>: one partial sum per column block, added at the end -- the summation order of the
+          // two-tile kernel, where the two blocks belong to different warps
+          float adot0 = 0.0f, adot = 0.0f;
+          for (int j = 0; j < nblk; ++j) {
+            if (j == 1) { adot0 = adot; adot = 0.0f; }
+            uint32_t v[64];
+            NB_TMEM_LD32(t_main + j * 64, v);
+            {
+              uint32_t* v2p = v + 32;
+              NB_TMEM_LD32(t_main + j * 64 + 32, v2p);
+            }
+            NB_TMEM_WAIT64(v);
+            if (j + 1 >= nblk) {  // last accumulator read of this stage: hand the TMEM columns back
+              tc_fence_before();
+              mbar_arrive(smem_u32(bar_drain + t));
+            }
+            const uint32_t rp = smem_u32(act_t) + j * kBlockBytes + row * 128;
+            if (st.alpha_dot) {
+              const uint32_t wa = smem_u32(bias_s) + (plan.alpha_w_off + j * 64) * 4;
+              epi_convert32<true>(v, 0, rp, wa, sw, relu, adot);
+              epi_convert32<true>(v, 32, rp, wa, sw, relu, adot);
+            } else if (relu) {
+              epi_convert32<false, 1>(v, 0, rp, 0u, sw, true, adot);
+              epi_convert32<false, 1>(v, 32, rp, 0u, sw, true, adot);
+            } else {
+              epi_convert32<false, 0>(v, 0, rp, 0u, sw, false, adot);
+              epi_convert32<false, 0>(v, 32, rp, 0u, sw, false, adot);
+            }
+            fence_async_smem();
+            mbar_arrive(smem_u32(bar_act + 2 * t + j));
+          }
+          if (st.alpha_dot) alpha_dot = adot0 + adot;
+          if (st.write_encd) {
+            encode_row<0, 8>(enc_t, row, v0, v1, v2, plan.Ld);
+            fence_async_smem();
+            mbar_arrive(smem_u32(bar_encd + t));
+          }
+        } else {
+          uint32_t v[4];
+          tmem_ld4(t_main, v);
+          tc_wait_ld();
+          float4 o;
+          o.x = __uint_as_float(v[0]) * kInvActScale + bs[0];
+          o.y = __uint_as_float(v[1]) * kInvActScale + bs[1];
+          o.z = __uint_as_float(v[2]) * kInvActScale + bs[2];
+          if (st.epi == EPI_RGB) o.w = alpha_dot * kInvActScale + bias_s[plan.alpha_b_off];
+          else o.w = __uint_as_float(v[3]) * kInvActScale + bs[3];
+          tc_fence_before();
+          mbar_arrive(smem_u32(bar_drain + t));
+          if (in_range) reinterpret_cast<float4*>(raw)[tile * kTileM + row] = o;
+        }
+      }
+    }
+  }
   tc_fence_before();
   __syncthreads();
   if (warp == 1) {
@@ -1010,6 +1293,24 @@ static size_t tc2_smem_bytes(const TcPlan& plan) {
   return b;
 }
 
+static size_t tc4_smem_bytes(const TcPlan& plan) {
+  size_t b = 1024;
+  b += (size_t)4 * (plan.n_act_blocks + 1) * kBlockBytes;
+  b += (size_t)kRing4 * kSlot4Bytes;
+  b += (size_t)((plan.n_bias + 3) & ~3) * sizeof(float);
+  b += (2 * kRing4 + 4 + 4 + 8 + 4 + 4) * sizeof(uint64_t) + 16;
+  b += (size_t)plan.n_steps * sizeof(uint4);
+  return b;
+}
+// graphs the four-tile kernel takes: at most two activation blocks per tile and every stage N <= 128
+static bool tc4_eligible(const TcPlan& plan) {
+  if (plan.n_act_blocks > 2 || tc4_smem_bytes(plan) > 227 * 1024) return false;
+  for (int s = 0; s < plan.n_stages; ++s)
+    if (plan.st[s].n_main > 128) return false;
+  return true;
+}
+static int g_fwd_4tile = 1;
+
 // NB_FWD_2CTA: 1 = inference launches use the CTA-pair kernel (mlp_tc2_kernel), 0 = the single-CTA kernel
 static int g_fwd_2cta = -1;
 static int fwd_2cta_mode() {
@@ -1056,6 +1357,8 @@ int packed_build(nb_model* m, cudaStream_t stream) {
       e = cudaFuncSetAttribute(mlp_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
     if (e == cudaSuccess)
       e = cudaFuncSetAttribute(mlp_tc2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+    if (e == cudaSuccess)
+      e = cudaFuncSetAttribute(mlp_tc4_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
     if (e != cudaSuccess) {
       packed_free(p);
       set_error("bf16 pack setup failed: %s", cudaGetErrorString(e));
@@ -1107,6 +1410,13 @@ int tc_forward(const nb_model* m, const float* rays, int ray_stride, const float
   }
   TcSrc src{rays, ray_stride, z_vals, n_samples > 0 ? n_samples : 1, pts, viewdirs, points_per_dir > 0 ? points_per_dir : 1};
   const int64_t n_tiles = ceil_div(n_points, kTileM);
+  if (rec == nullptr && g_fwd_4tile != 0 && tc4_eligible(p->plan)) {
+    // narrow graph (every stage N <= 128): four tiles in flight per CTA
+    const int grid4 = (int)std::min<int64_t>(ceil_div(n_tiles, 4), sm_count());
+    mlp_tc4_kernel<<<grid4, kThreadsTc4, tc4_smem_bytes(p->plan), stream>>>(p->plan, p->d_w, p->d_bias, src, (long long)n_points, raw);
+    NB_LAUNCHED();
+    return NB_OK;
+  }
   if (rec == nullptr && fwd_2cta_mode() != 0 && tc2_smem_bytes(p->plan) <= 227 * 1024) {
     // CTA-pair kernel: clusters of 2 CTAs, four tiles per cluster round
     const int clusters = (int)std::min<int64_t>(ceil_div(n_tiles, 4), sm_count() / 2);
@@ -1137,6 +1447,11 @@ extern "C" int nb_set_option(const char* name, int value) {
   using namespace nb;
   NB_REQUIRE(name != nullptr, "nb_set_option: null name");
   if (strcmp(name, "fwd_2cta") == 0) return set_fwd_2cta(value);
+  if (strcmp(name, "fwd_4tile") == 0) {
+    const int old = g_fwd_4tile;
+    g_fwd_4tile = value != 0;
+    return old;
+  }
   if (strcmp(name, "bwd_sm_reserve") == 0) {
     const int old = g_bwd_sm_reserve;
     g_bwd_sm_reserve = value < 0 ? 0 : (value > 64 ? 64 : value);
