@@ -85,8 +85,9 @@ struct Gemm {
   int64_t M; int N; int64_t K;
   const float* bias;          // [N] or null
   const float* mask; int64_t ldm;  // multiply by (mask[i][j] > 0) when non-null
-  int relu, accumulate, atomic;
+  int relu, accumulate;
   int64_t k_split;            // contraction elements per blockIdx.z
+  int64_t c_split;            // C elements between the partial results of consecutive blockIdx.z (split-K), else 0
 };
 
 constexpr int BM = 128, BN = 128, BK = 16, PAD = 4;
@@ -174,11 +175,7 @@ __global__ void __launch_bounds__(256) sgemm_kernel(Gemm g) {
       const int gj = j0 + (b < 4 ? tx * 4 + b : 64 + tx * 4 + (b - 4));
       if (gj >= g.N) continue;
       float v = acc[a][b];
-      float* cp = g.C + gi * g.ldc + gj;
-      if (g.atomic) {
-        atomicAdd(cp, v);
-        continue;
-      }
+      float* cp = g.C + (int64_t)blockIdx.z * g.c_split + gi * g.ldc + gj;
       if (g.accumulate) v += *cp;
       if (g.bias != nullptr) v += g.bias[gj];
       if (g.relu) v = fmaxf(v, 0.f);
@@ -193,7 +190,10 @@ static int launch_gemm(int amode, int bmode, Gemm g, int splits, cudaStream_t s)
   if (splits < 1) splits = 1;
   g.k_split = round_up(ceil_div(g.K, splits), BK);
   const int z = (int)ceil_div(g.K, g.k_split);
-  g.atomic = (z > 1 || g.atomic) ? 1 : 0;
+  if (z > 1 && g.c_split == 0) {
+    set_error("launch_gemm: split-K needs a partial-result buffer");
+    return NB_ERR_INVALID;
+  }
   dim3 grid((unsigned)ceil_div(g.M, BM), (unsigned)ceil_div(g.N, BN), (unsigned)z);
   if (amode == 0 && bmode == 0) sgemm_kernel<0, 0><<<grid, 256, 0, s>>>(g);
   else if (amode == 0 && bmode == 1) sgemm_kernel<0, 1><<<grid, 256, 0, s>>>(g);
@@ -203,9 +203,31 @@ static int launch_gemm(int amode, int bmode, Gemm g, int splits, cudaStream_t s)
   return NB_OK;
 }
 
-// db[j] += sum_i dY[i][j]
+// dst[i][j] += part[0][i][j] + part[1][i][j] + ... in that order: the split-K partial results of a weight gradient (or
+// the per-block partial column sums of a bias gradient) are summed by one thread per element, so a gradient is the same
+// bits on every run (atomics would make the order a race)
+__global__ void ordered_sum_kernel(const float* __restrict__ part, int n_parts, int64_t part_stride, int rows, int cols,
+                                   float* __restrict__ dst, int64_t ld) {
+  const int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= (int64_t)rows * cols) return;
+  float v = part[e];
+  for (int q = 1; q < n_parts; ++q) v += part[q * part_stride + e];
+  dst[(e / cols) * ld + (e % cols)] += v;
+}
+
+static int launch_ordered_sum(const float* part, int n_parts, int64_t part_stride, int rows, int cols, float* dst,
+                              int64_t ld, cudaStream_t s) {
+  const int64_t n = (int64_t)rows * cols;
+  ordered_sum_kernel<<<(unsigned)ceil_div(n, 256), 256, 0, s>>>(part, n_parts, part_stride, rows, cols, dst, ld);
+  NB_LAUNCHED();
+  return NB_OK;
+}
+
+constexpr int64_t kColsumRows = 2048;  // rows per block of colsum_kernel
+
+// part[blockIdx.x][j] = sum of dY[i][j] over the block's rows; db[j] += the partials in block order (ordered_sum_kernel)
 __global__ void colsum_kernel(const float* __restrict__ dY, int64_t ld, int64_t M, int N, int64_t rows_per_block,
-                              float* __restrict__ db) {
+                              float* __restrict__ part) {
   const int j = blockIdx.y * 32 + (threadIdx.x & 31);
   const int sub = threadIdx.x >> 5;  // 8 row lanes
   const int64_t r0 = (int64_t)blockIdx.x * rows_per_block;
@@ -213,24 +235,24 @@ __global__ void colsum_kernel(const float* __restrict__ dY, int64_t ld, int64_t 
   float acc = 0.f;
   if (j < N)
     for (int64_t i = r0 + sub; i < r1; i += 8) acc += dY[i * ld + j];
-  __shared__ float part[8][33];
-  part[sub][threadIdx.x & 31] = acc;
+  __shared__ float lanes[8][33];
+  lanes[sub][threadIdx.x & 31] = acc;
   __syncthreads();
   if (sub == 0 && j < N) {
     float v = 0.f;
 #pragma unroll
-    for (int q = 0; q < 8; ++q) v += part[q][threadIdx.x & 31];
-    atomicAdd(db + j, v);
+    for (int q = 0; q < 8; ++q) v += lanes[q][threadIdx.x & 31];
+    part[(int64_t)blockIdx.x * N + j] = v;
   }
 }
 
-static int launch_colsum(const float* dY, int64_t ld, int64_t M, int N, float* db, cudaStream_t s) {
+static int launch_colsum(const float* dY, int64_t ld, int64_t M, int N, float* db, float* part, cudaStream_t s) {
   if (M <= 0) return NB_OK;
-  const int64_t rows_per_block = 2048;
-  dim3 grid((unsigned)ceil_div(M, rows_per_block), (unsigned)ceil_div(N, 32));
-  colsum_kernel<<<grid, 256, 0, s>>>(dY, ld, M, N, rows_per_block, db);
+  const int blocks = (int)ceil_div(M, kColsumRows);
+  dim3 grid((unsigned)blocks, (unsigned)ceil_div(N, 32));
+  colsum_kernel<<<grid, 256, 0, s>>>(dY, ld, M, N, kColsumRows, part);
   NB_LAUNCHED();
-  return NB_OK;
+  return launch_ordered_sum(part, blocks, N, 1, N, db, N, s);
 }
 
 __global__ void copy_cols_kernel(const float* __restrict__ src, int64_t lds, float* __restrict__ dst, int64_t ldd,
@@ -248,7 +270,7 @@ struct Fp32Layout {
   bool save = false;
   int ldx = 0, ldd = 0;
   size_t off_ex = 0, off_ed = 0, off_h = 0, off_feat = 0, off_dirh = 0, off_g0 = 0, off_g1 = 0, off_gfeat = 0,
-         off_gdir = 0, total = 0;
+         off_gdir = 0, off_part = 0, total = 0;
   int n_h = 0;
 };
 
@@ -278,6 +300,11 @@ static Fp32Layout fp32_layout(const Graph& g, int64_t n_points, bool save) {
     L.off_g1 = take((size_t)L.P * g.width);
     L.off_gfeat = take((size_t)L.P * std::max(g.feat_width, 1));
     L.off_gdir = take((size_t)L.P * std::max(g.dir_width, 1));
+    // partial results of the gradient reductions (split-K weight gradients: splits x tiles <= 2 x SMs tiles of BM x BN;
+    // bias gradients: one row per 2048 points), summed in a fixed order by ordered_sum_kernel
+    L.off_part = take(std::max<size_t>((size_t)2 * sm_count() * BM * BN,
+                                       (size_t)ceil_div(L.P, kColsumRows) *
+                                           std::max(std::max(g.width, g.feat_width), std::max(g.dir_width, 4))));
   }
   L.total = off;
   return L;
@@ -387,12 +414,17 @@ static int fp32_forward(const nb_model* m, EncodeSrc src, int64_t n_points, floa
 // ------------------------------------------------------------------------------------ backward
 // wgrad: dW[out, in_off : in_off+Kin] += dY[P, out]^T . X[P, Kin]   (contraction over the points)
 static int wgrad(const float* dY, int64_t ldy, int out, const float* X, int64_t ldx, int Kin, float* dW, int64_t ldw,
-                 int64_t P, cudaStream_t s) {
+                 int64_t P, float* part, cudaStream_t s) {
   Gemm q{};
-  q.A = dY; q.lda = ldy; q.B = X; q.ldb = ldx; q.C = dW; q.ldc = ldw; q.M = out; q.N = Kin; q.K = P; q.atomic = 1;
+  q.A = dY; q.lda = ldy; q.B = X; q.ldb = ldx; q.C = part; q.ldc = Kin; q.M = out; q.N = Kin; q.K = P;
+  q.c_split = (int64_t)out * Kin;
   const int tiles = (int)(ceil_div(out, BM) * ceil_div(Kin, BN));
   int splits = (int)std::min<int64_t>(std::max<int64_t>(1, (2 * sm_count()) / tiles), ceil_div(P, 512));
-  return launch_gemm(1, 1, q, splits, s);
+  const int64_t k_split = round_up(ceil_div(P, splits), BK);
+  const int z = (int)ceil_div(P, k_split);
+  int rc = launch_gemm(1, 1, q, splits, s);
+  if (rc != NB_OK) return rc;
+  return launch_ordered_sum(part, z, q.c_split, out, Kin, dW, ldw, s);
 }
 
 // dgrad: dX[P, Kin] (=|+=) (dY[P, out] . W[out, in_off : in_off+Kin]) * (mask > 0)
@@ -421,6 +453,7 @@ static int fp32_backward(const nb_model* m, int64_t P, float* d_raw, void* ws, s
   float* G[2] = {wsf(ws, L.off_g0), wsf(ws, L.off_g1)};
   float* GFEAT = wsf(ws, L.off_gfeat);
   float* GDIR = wsf(ws, L.off_gdir);
+  float* PART = wsf(ws, L.off_part);
   auto hbuf = [&](int i) { return H + (size_t)i * L.P * g.width; };
   const int D = g.depth;
   const float* HL = hbuf(D - 1);
@@ -434,42 +467,42 @@ static int fp32_backward(const nb_model* m, int64_t P, float* d_raw, void* ws, s
     const Lin& ld = g.lins[g.dir];
     const Lin& lr = g.lins[g.rgb];
     // rgb head
-    NB_TRY(wgrad(d_raw, 4, 3, DIRH, g.dir_width, lr.in, grad + lr.w_off, lr.in, P, s));
-    NB_TRY(launch_colsum(d_raw, 4, P, 3, grad + lr.b_off, s));
+    NB_TRY(wgrad(d_raw, 4, 3, DIRH, g.dir_width, lr.in, grad + lr.w_off, lr.in, P, PART, s));
+    NB_TRY(launch_colsum(d_raw, 4, P, 3, grad + lr.b_off, PART, s));
     NB_TRY(dgrad(d_raw, 4, 3, W + lr.w_off, lr.in, lr.in, GDIR, g.dir_width, P, DIRH, g.dir_width, 0, s));
     // dir layer
-    NB_TRY(wgrad(GDIR, g.dir_width, ld.out, FEAT, g.feat_width, g.feat_width, grad + ld.w_off, ld.in, P, s));
+    NB_TRY(wgrad(GDIR, g.dir_width, ld.out, FEAT, g.feat_width, g.feat_width, grad + ld.w_off, ld.in, P, PART, s));
     if (g.Cd > 0)
-      NB_TRY(wgrad(GDIR, g.dir_width, ld.out, ED, L.ldd, g.Cd, grad + ld.w_off + g.feat_width, ld.in, P, s));
-    NB_TRY(launch_colsum(GDIR, g.dir_width, P, ld.out, grad + ld.b_off, s));
+      NB_TRY(wgrad(GDIR, g.dir_width, ld.out, ED, L.ldd, g.Cd, grad + ld.w_off + g.feat_width, ld.in, P, PART, s));
+    NB_TRY(launch_colsum(GDIR, g.dir_width, P, ld.out, grad + ld.b_off, PART, s));
     NB_TRY(dgrad(GDIR, g.dir_width, ld.out, W + ld.w_off, ld.in, g.feat_width, GFEAT, g.feat_width, P,
                  g.feat_act ? FEAT : nullptr, g.feat_width, 0, s));
     // feat / bottleneck
-    NB_TRY(wgrad(GFEAT, g.feat_width, lf.out, HL, g.width, lf.in, grad + lf.w_off, lf.in, P, s));
-    NB_TRY(launch_colsum(GFEAT, g.feat_width, P, lf.out, grad + lf.b_off, s));
+    NB_TRY(wgrad(GFEAT, g.feat_width, lf.out, HL, g.width, lf.in, grad + lf.w_off, lf.in, P, PART, s));
+    NB_TRY(launch_colsum(GFEAT, g.feat_width, P, lf.out, grad + lf.b_off, PART, s));
     NB_TRY(dgrad(GFEAT, g.feat_width, lf.out, W + lf.w_off, lf.in, lf.in, G[cur], g.width, P, nullptr, 0, 0, s));
     // alpha head (sums into the same dH, then the ReLU mask of the last trunk layer)
-    NB_TRY(wgrad(d_raw + 3, 4, 1, HL, g.width, la.in, grad + la.w_off, la.in, P, s));
-    NB_TRY(launch_colsum(d_raw + 3, 4, P, 1, grad + la.b_off, s));
+    NB_TRY(wgrad(d_raw + 3, 4, 1, HL, g.width, la.in, grad + la.w_off, la.in, P, PART, s));
+    NB_TRY(launch_colsum(d_raw + 3, 4, P, 1, grad + la.b_off, PART, s));
     NB_TRY(dgrad(d_raw + 3, 4, 1, W + la.w_off, la.in, la.in, G[cur], g.width, P, maskL, g.width, 1, s));
   } else {
     const Lin& lo = g.lins[g.out4];
-    NB_TRY(wgrad(d_raw, 4, 4, HL, g.width, lo.in, grad + lo.w_off, lo.in, P, s));
-    NB_TRY(launch_colsum(d_raw, 4, P, 4, grad + lo.b_off, s));
+    NB_TRY(wgrad(d_raw, 4, 4, HL, g.width, lo.in, grad + lo.w_off, lo.in, P, PART, s));
+    NB_TRY(launch_colsum(d_raw, 4, P, 4, grad + lo.b_off, PART, s));
     NB_TRY(dgrad(d_raw, 4, 4, W + lo.w_off, lo.in, lo.in, G[cur], g.width, P, maskL, g.width, 0, s));
   }
   for (int i = D - 1; i >= 0; --i) {
     const Lin& l = g.lins[g.trunk[i]];
     const float* dZ = G[cur];
-    NB_TRY(launch_colsum(dZ, g.width, P, l.out, grad + l.b_off, s));
+    NB_TRY(launch_colsum(dZ, g.width, P, l.out, grad + l.b_off, PART, s));
     if (i == 0) {
-      NB_TRY(wgrad(dZ, g.width, l.out, EX, L.ldx, g.Cx, grad + l.w_off, l.in, P, s));
+      NB_TRY(wgrad(dZ, g.width, l.out, EX, L.ldx, g.Cx, grad + l.w_off, l.in, P, PART, s));
       break;
     }
     const bool cat = (i - 1 == g.skip);
     const int off = cat ? g.Cx : 0;
-    if (cat) NB_TRY(wgrad(dZ, g.width, l.out, EX, L.ldx, g.Cx, grad + l.w_off, l.in, P, s));
-    NB_TRY(wgrad(dZ, g.width, l.out, hbuf(i - 1), g.width, g.width, grad + l.w_off + off, l.in, P, s));
+    if (cat) NB_TRY(wgrad(dZ, g.width, l.out, EX, L.ldx, g.Cx, grad + l.w_off, l.in, P, PART, s));
+    NB_TRY(wgrad(dZ, g.width, l.out, hbuf(i - 1), g.width, g.width, grad + l.w_off + off, l.in, P, PART, s));
     const float* mk = layer_has_relu(g, i - 1) ? hbuf(i - 1) : nullptr;
     NB_TRY(dgrad(dZ, g.width, l.out, W + l.w_off + off, l.in, g.width, G[cur ^ 1], g.width, P, mk, g.width, 0, s));
     cur ^= 1;

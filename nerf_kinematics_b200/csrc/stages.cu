@@ -463,6 +463,13 @@ int nb_posenc(const float* x, int64_t n, int L, int include_input, float* out, i
 int nb_mse_loss(const float* pred, const float* tgt, int64_t count, float grad_scale, float* loss, float* d_pred,
                 nb_stream_t stream) {
   NB_REQUIRE(count > 0 && pred && tgt && loss, "nb_mse_loss: bad arguments");
+  if (count <= (1 << 16)) {
+    // a training batch (N_rand <= 21 845 rays): one block, so the sum has one order and the loss is the same bits on
+    // every run; larger inputs (whole images) spread over the machine and combine their block sums atomically
+    mse_kernel<<<1, 1024, 0, as_stream(stream)>>>(pred, tgt, count, grad_scale, loss, d_pred);
+    NB_LAUNCHED();
+    return NB_OK;
+  }
   int blocks = (int)std::min<int64_t>(ceil_div(count, 256), 4 * sm_count());
   mse_kernel<<<blocks, 256, 0, as_stream(stream)>>>(pred, tgt, count, grad_scale, loss, d_pred);
   NB_LAUNCHED();
