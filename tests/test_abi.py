@@ -113,3 +113,16 @@ def test_compute_fails_loudly_without_gpu():
         m.query(torch.zeros(2, 4, 3), torch.zeros(2, 3))
     with pytest.raises(NotImplementedError):
         m(torch.zeros(2, 66))
+
+
+def test_options_round_trip_without_a_gpu():
+    """nb_set_option returns the previous value and rejects unknown names (include/nerf_b200.h); no device needed."""
+    L = _lib.lib()
+    for name, new in ((b"fwd_4tile", 0), (b"fwd_2cta", 1), (b"bwd_sm_reserve", 5)):
+        old = L.nb_set_option(name, new)
+        assert old >= 0
+        assert L.nb_set_option(name, old) == new
+        assert L.nb_set_option(name, old) == old
+    assert L.nb_set_option(b"no_such_option", 1) == -1
+    assert b"no_such_option" in L.nb_last_error()
+    assert abs(L.nb_mlp_activation_scale() - 2.0 ** -5) == 0.0
