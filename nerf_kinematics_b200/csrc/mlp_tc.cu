@@ -1452,6 +1452,7 @@ extern "C" int nb_set_option(const char* name, int value) {
     g_fwd_4tile = value != 0;
     return old;
   }
+  if (strcmp(name, "composite_lc") == 0) return set_composite_lc(value);
   if (strcmp(name, "bwd_sm_reserve") == 0) {
     const int old = g_bwd_sm_reserve;
     g_bwd_sm_reserve = value < 0 ? 0 : (value > 64 ? 64 : value);

@@ -99,7 +99,7 @@ def main():
         bytes_ray = (S_ * 16 + S_ * 4 + 12) + (S_ * 4 if tag == "coarse" else 0) + 24
         gbs = n * bytes_ray / med / 1e9
         print("composite_fwd %-6s %8.3f ms  %8.1f GB/s  frac(of measured %.0f)=%.3f" % (tag, med * 1e3, gbs, pk["hbm_gbs"], gbs / pk["hbm_gbs"]))
-        if tag == "fine":
+        if True:
             g = torch.randn(n, 3, device=dev)
             med, _ = timeit(lambda: ops.composite_backward(raw, z, rays, None, True, g), a.reps, flush, inner=4)
             gbs = n * (S_ * 20 + 24 + S_ * 16) / med / 1e9
