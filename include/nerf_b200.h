@@ -287,6 +287,20 @@ size_t nb_render_workspace_bytes(const nb_model_t* coarse, const nb_model_t* fin
 int nb_render_rays(const nb_model_t* coarse, const nb_model_t* fine, const float* rays, int ray_stride, int64_t n,
                    const nb_render_cfg* cfg, const nb_render_rand* rnd, const nb_render_out* out, void* workspace,
                    size_t workspace_bytes, nb_stream_t stream);
+/* nb_render_rays without a caller workspace and without any allocation.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving
+ * loops, harnesses that forbid it).  The chunk's intermediates live in a file-scope `static __device__` array of
+ * nb_render_static_scratch_bytes() = 16 MiB inside the library (held by every GPU that loads it until the process exits);
+ * about 3 000 rays at 64 + 128 samples on the 16-bit path.  Inference only (cfg->save_for_backward must be 0); a call
+ * whose intermediates exceed the array fails with NB_ERR_WORKSPACE and a message stating both sizes.  The call makes
+ * no cudaMalloc / cudaFree and uses no allocating library routine; models must have been packed before (nb_model_pack).
+ * All calls on a device share the array, which keeps the last call's contents (every region is written before it is
+ * read, nothing needs clearing): calls that overlap on the GPU (different streams) RACE -- serialise them.
+ * Results equal nb_render_rays on the same inputs bit for bit (same kernels, same order). */
+size_t nb_render_static_scratch_bytes(void);
+int nb_render_rays_static(const nb_model_t* coarse, const nb_model_t* fine, const float* rays, int ray_stride, int64_t n,
+                          const nb_render_cfg* cfg, const nb_render_rand* rnd, const nb_render_out* out,
+                          nb_stream_t stream);
 /* Autograd of the call above w.r.t. the network parameters (TF train():807-826 / PT train_nerf.py:286):
  * compositing backward and MLP backward for the fine and the coarse pass; no gradient flows through
  * sample_pdf (stop_gradient, run_nerf.py:218 / detach, train_utils.py:103).  Same rays / cfg / rnd / workspace

@@ -88,6 +88,9 @@ SIGNATURES = {
                              sz, p]),
     "nb_render_rays_backward": (i32, [p, p, p, i32, i64, C.POINTER(RenderCfg), C.POINTER(RenderRand),
                                       C.POINTER(RenderGrads), p, sz, p, p, p]),
+    "nb_render_static_scratch_bytes": (sz, []),
+    "nb_render_rays_static": (i32, [p, p, p, i32, i64, C.POINTER(RenderCfg), C.POINTER(RenderRand), C.POINTER(RenderOut),
+                                    p]),
 }
 
 _lock = threading.Lock()

@@ -6,6 +6,12 @@
 
 #include "model.h"
 
+// Scratch of nb_render_rays_static (end of this file): lives in the library image, so the entry point allocates nothing.
+// Every GPU that loads the library holds these bytes until the process exits.  In HOST code the name below is a host-side
+// stand-in, not a device address: the host takes its address once per device with cudaGetSymbolAddress.
+#define NB_STATIC_SCRATCH_BYTES (16u << 20)
+static __device__ __align__(256) unsigned char g_static_scratch[NB_STATIC_SCRATCH_BYTES];
+
 namespace nb {
 
 struct RenderLayout {
@@ -185,6 +191,43 @@ int nb_render_rays_backward(const nb_model_t* coarse, const nb_model_t* fine, co
     NB_TRY(nb_mlp_backward(coarse, cfg->precision, n * S, draw, mlp_c, L.mlp_c_bytes, grad_coarse, stream));
   }
   return NB_OK;
+}
+
+size_t nb_render_static_scratch_bytes(void) { return (size_t)NB_STATIC_SCRATCH_BYTES; }
+
+// nb_render_rays for callers that cannot allocate (CUDA graph capture, serving loops): the chunk's intermediates go to
+// g_static_scratch instead of a caller workspace.  Inference only.  The call itself makes no cudaMalloc / cudaFree and
+// uses no allocating library routine; the models must have been packed beforehand (nb_model_pack, set-up time).
+// Every region of the scratch is written by this call before it is read (depths, raw network output, weights), so nothing
+// has to start at zero and the previous call's contents do not matter.  All calls on a device share the one array: two
+// calls that overlap on the GPU (different streams) race.
+int nb_render_rays_static(const nb_model_t* coarse, const nb_model_t* fine, const float* rays, int ray_stride, int64_t n,
+                          const nb_render_cfg* cfg, const nb_render_rand* rnd, const nb_render_out* out,
+                          nb_stream_t stream) {
+  NB_TRY(check_cfg(coarse, ray_stride, n, cfg));
+  NB_REQUIRE(!cfg->save_for_backward, "nb_render_rays_static: inference only (save_for_backward must be 0)");
+  const size_t need = render_layout(coarse, fine, n, *cfg).total;
+  if (need > (size_t)NB_STATIC_SCRATCH_BYTES) {
+    set_error("nb_render_rays_static: %lld rays need %zu bytes of scratch, the static array holds %zu (render fewer rays per "
+              "call or use nb_render_rays with a workspace)", (long long)n, need, (size_t)NB_STATIC_SCRATCH_BYTES);
+    return NB_ERR_WORKSPACE;
+  }
+  // device address of the array, once per device, with that device current
+  constexpr int kMaxDev = 64;
+  static void* addr[kMaxDev] = {};
+  int dev = -1;
+  NB_CUDA(cudaGetDevice(&dev));
+  NB_REQUIRE(dev >= 0 && dev < kMaxDev, "nb_render_rays_static: device ordinal %d out of range", dev);
+  if (addr[dev] == nullptr) {
+    void* p = nullptr;
+    const cudaError_t e = cudaGetSymbolAddress(&p, g_static_scratch);
+    if (e != cudaSuccess || p == nullptr) {
+      set_error("nb_render_rays_static: cudaGetSymbolAddress failed: %s", cudaGetErrorString(e));
+      return NB_ERR_CUDA;
+    }
+    addr[dev] = p;
+  }
+  return nb_render_rays(coarse, fine, rays, ray_stride, n, cfg, rnd, out, addr[dev], (size_t)NB_STATIC_SCRATCH_BYTES, stream);
 }
 
 }  // extern "C"
