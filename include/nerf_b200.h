@@ -70,6 +70,8 @@ void nb_launch_count_reset(void);
  *               every weight slot), 0 = the single-CTA kernel.  Initial value: environment NB_FWD_2CTA, else 0.
  *   "fwd_4tile": 1 (default) = inference launches of graphs whose stages are all N <= 128 (FlexibleNeRFModel 4x128) use the
  *               four-tiles-per-CTA kernel, 0 = the two-tile kernel.
+ *   "composite_lc": 1 (default) = compositing of 64 / 128 / 192 samples per ray uses the lane-contiguous bulk-copy kernels,
+ *               0 = the strided kernels for every sample count.
  *   "bwd_sm_reserve": number of SMs (0..64) the persistent backward kernels of the tensor-core train path leave free, so
  *               that a gradient all-reduce enqueued on another stream can run under them (data-parallel step). */
 int nb_set_option(const char* name, int value);
