@@ -54,6 +54,7 @@ def main():
     ap.add_argument("--reps", type=int, default=10)
     ap.add_argument("--model", default="tf", choices=["tf", "flexible"])
     ap.add_argument("--only-mlp", action="store_true", help="just the 16-bit fused MLP kernel (short run for ncu)")
+    ap.add_argument("--only-stages", action="store_true", help="skip the MLP kernels")
     a = ap.parse_args()
     pk = peaks()
     dev = torch.device("cuda:0")
@@ -65,7 +66,7 @@ def main():
     rays = ops.make_ray_batch(o, d, 2.0, 6.0, use_viewdirs=True)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)  # > 126 MB L2
     res = {}
-    for S_ in ((S + I,) if a.only_mlp else (S, S + I)):
+    for S_ in (() if a.only_stages else (S + I,) if a.only_mlp else (S, S + I)):
         z = ops.sample_coarse(rays, S_)
         raw = torch.empty(n, S_, 4, device=dev)
         for prec_name in (("bf16",) if a.only_mlp else ("bf16", "fp32")):
