@@ -72,6 +72,8 @@ void nb_launch_count_reset(void);
  *               four-tiles-per-CTA kernel, 0 = the two-tile kernel.
  *   "composite_lc": 1 (default) = compositing of 64 / 128 / 192 samples per ray uses the lane-contiguous bulk-copy kernels,
  *               0 = the strided kernels for every sample count.
+ *   "sample_fine2": 1 (default) = nb_sample_fine / the chunk renderer with 64 depths, 128 or 64 deterministic samples and
+ *               16-byte aligned rows use the two-rays-per-warp kernel, 0 = the one-ray-per-warp kernel (bit-identical).
  *   "bwd_sm_reserve": number of SMs (0..64) the persistent backward kernels of the tensor-core train path leave free, so
  *               that a gradient all-reduce enqueued on another stream can run under them (data-parallel step). */
 int nb_set_option(const char* name, int value);

@@ -49,6 +49,7 @@ static inline int64_t ceil_div(int64_t a, int64_t b) { return (a + b - 1) / b; }
 static inline int64_t round_up(int64_t a, int64_t b) { return ceil_div(a, b) * b; }
 
 int sm_count();  // SMs of the current device (cached)
+int set_sample_fine2(int v);  // volume.cu: 0 = one-ray-per-warp sample_fine kernel only; returns the previous value
 int set_composite_lc(int v);  // volume.cu: 0 = strided compositing kernels only; returns the previous value
 
 // ---- device helpers

@@ -1453,6 +1453,7 @@ extern "C" int nb_set_option(const char* name, int value) {
     return old;
   }
   if (strcmp(name, "composite_lc") == 0) return set_composite_lc(value);
+  if (strcmp(name, "sample_fine2") == 0) return set_sample_fine2(value);
   if (strcmp(name, "bwd_sm_reserve") == 0) {
     const int old = g_bwd_sm_reserve;
     g_bwd_sm_reserve = value < 0 ? 0 : (value > 64 ? 64 : value);
