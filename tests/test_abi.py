@@ -118,7 +118,7 @@ def test_compute_fails_loudly_without_gpu():
 def test_options_round_trip_without_a_gpu():
     """nb_set_option returns the previous value and rejects unknown names (include/nerf_b200.h); no device needed."""
     L = _lib.lib()
-    for name, new in ((b"fwd_4tile", 0), (b"fwd_2cta", 1), (b"bwd_sm_reserve", 5)):
+    for name, new in ((b"fwd_4tile", 0), (b"fwd_2cta", 1), (b"bwd_sm_reserve", 5), (b"composite_lc", 0), (b"sample_fine2", 0)):
         old = L.nb_set_option(name, new)
         assert old >= 0
         assert L.nb_set_option(name, old) == new

@@ -214,6 +214,39 @@ def test_sample_fine_merge_and_std():
     assert torch.equal(m.cpu(), ref)
 
 
+def test_sample_fine_two_ray_kernel_equals_one_ray_kernel():
+    """The two-rays-per-warp kernel (64 depths, 128 / 64 deterministic samples; csrc/volume.cu sample_fine2_kernel) against
+    the one-ray-per-warp kernel it replaces, bit for bit: peaked, flat and floor-dominated weights, repeated depths (the
+    rank fix-up walk), an odd ray count (a warp's second ray missing) and every optional output."""
+    from nerf_kinematics_b200._lib import lib
+    gen = torch.Generator().manual_seed(5)
+    n = 4097
+    z = torch.sort(torch.rand(n, 64, generator=gen) * 4 + 2, -1)[0]
+    z[::5] = torch.linspace(2.0, 6.0, 64)                       # the render path's depths
+    z[3::11, 20:24] = z[3::11, 20:21]                           # repeated depths
+    z[7::13, 40:] = z[7::13, 40:41]                             # a constant tail (zero-width bins)
+    w = torch.rand(n, 64, generator=gen) ** 6
+    w[::7] = 0.0                                                # only the 1e-5 floor: a uniform pdf
+    w[1::7] *= 1e-6
+    w[2::7, :30] = 0.0                                          # mass behind an empty front
+    w[4::7, 33] = 50.0                                          # one dominant bin
+    z, w = z.to(DEV), w.to(DEV)
+    for ns in (128, 64):
+        res = {}
+        for v in (0, 1):
+            old = lib().nb_set_option(b"sample_fine2", v)
+            try:
+                res[v] = (ops.sample_fine(z, w, ns, want_samples=True, want_std=True), ops.sample_fine(z, w, ns))
+            finally:
+                lib().nb_set_option(b"sample_fine2", old)
+        (zf0, zs0, sd0), (zf0b, _, _) = res[0]
+        (zf1, zs1, sd1), (zf1b, _, _) = res[1]
+        assert torch.equal(zf1, zf0) and torch.equal(zs1, zs0) and torch.equal(zf1b, zf0)
+        assert maxdiff(sd1, sd0) <= 2e-6                        # a different summation order
+        ref, _ = torch.sort(torch.cat((z, zs1), -1), -1)
+        assert torch.equal(zf1, ref)
+
+
 def test_mse_loss():
     g = torch.Generator().manual_seed(3)
     a, b = torch.rand(1000, 3, generator=g), torch.rand(1000, 3, generator=g)
