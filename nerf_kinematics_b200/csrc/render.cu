@@ -15,7 +15,7 @@ static __device__ __align__(256) unsigned char g_static_scratch[NB_STATIC_SCRATC
 namespace nb {
 
 struct RenderLayout {
-  size_t off_zc = 0, off_rawc = 0, off_wc = 0, off_zf = 0, off_rawf = 0, off_scratch = 0, off_draw = 0, off_mlp_c = 0,
+  size_t off_zc = 0, off_rawc = 0, off_wc = 0, off_zf = 0, off_rawf = 0, off_scratch = 0, off_draw = 0, off_draw_c = 0, off_mlp_c = 0,
          off_mlp_f = 0, mlp_c_bytes = 0, mlp_f_bytes = 0, total = 0;
 };
 
@@ -42,6 +42,9 @@ static RenderLayout render_layout(const nb_model* coarse, const nb_model* fine, 
   L.mlp_f_bytes = I > 0 ? nb_mlp_workspace_bytes(mf, c.precision, nn * (S + I), c.save_for_backward) : 0;
   if (c.save_for_backward) {
     L.off_draw = take(sizeof(float) * nn * (S + I) * 4);
+    // the coarse pass's d_raw has its own buffer: the two networks' backward passes share nothing, so a caller may run
+    // them as two calls on two streams (trainer.py does, inside its captured step)
+    L.off_draw_c = I > 0 ? take(sizeof(float) * nn * S * 4) : L.off_draw;
     L.off_mlp_c = take(L.mlp_c_bytes);
     L.off_mlp_f = take(L.mlp_f_bytes);
   } else {
@@ -169,6 +172,7 @@ int nb_render_rays_backward(const nb_model_t* coarse, const nb_model_t* fine, co
   const int S = cfg->n_samples, I = cfg->n_importance;
   const bool hier = I > 0;
   float* draw = at(ws, L.off_draw);
+  float* draw_c = at(ws, L.off_draw_c);
   void* mlp_c = static_cast<char*>(ws) + L.off_mlp_c;
   void* mlp_f = static_cast<char*>(ws) + L.off_mlp_f;
   if (hier) {
@@ -182,8 +186,8 @@ int nb_render_rays_backward(const nb_model_t* coarse, const nb_model_t* fine, co
     }
     if (g->d_rgb0 || g->d_disp0 || g->d_acc0 || g->d_depth0) {
       NB_TRY(composite_backward_impl(at(ws, L.off_rawc), at(ws, L.off_zc), rays, ray_stride, n, S, r.noise_c,
-                                   rr.noise_c, cfg->white_bkgd, g->d_rgb0, g->d_disp0, g->d_acc0, g->d_depth0, draw, stream));
-      NB_TRY(nb_mlp_backward(coarse, cfg->precision, n * S, draw, mlp_c, L.mlp_c_bytes, grad_coarse, stream));
+                                   rr.noise_c, cfg->white_bkgd, g->d_rgb0, g->d_disp0, g->d_acc0, g->d_depth0, draw_c, stream));
+      NB_TRY(nb_mlp_backward(coarse, cfg->precision, n * S, draw_c, mlp_c, L.mlp_c_bytes, grad_coarse, stream));
     }
   } else if (g->d_rgb || g->d_disp || g->d_acc || g->d_depth) {
     NB_TRY(composite_backward_impl(at(ws, L.off_rawc), at(ws, L.off_zc), rays, ray_stride, n, S, r.noise_c,

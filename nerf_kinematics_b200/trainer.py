@@ -85,6 +85,8 @@ class TrainStep:
         # NCCL collective itself (NB_SPLIT_GRAPH=0) measured the same step time on 2 B200 but left the process group
         # unable to shut down cleanly.
         self._split_graph = bool(int(os.environ.get("NB_SPLIT_GRAPH", "1")))
+        self._bwd_streams = bool(int(os.environ.get("NB_BWD_STREAMS", "1")))
+        self._side = None
         self._overlap = bool(int(os.environ.get("NB_OVERLAP_ALLREDUCE", "1")))
         # the backward kernels are persistent, one 215 KB CTA per SM: leave a few SMs to NCCL so that the fine network's
         # all-reduce really runs under the coarse network's backward (NB_BWD_SM_RESERVE, default 8 when world > 1)
@@ -185,7 +187,7 @@ class TrainStep:
         scale = 1.0 / self.world  # the mean over the global batch: each rank contributes its share
         with torch.cuda.device(dev):
             st = _stream()
-            if phase != 2:
+            if phase not in (2, "coarse", "fine"):
                 check(lib().nb_render_rays(hc, hf, C.c_void_p(rays.data_ptr()), stride, n, C.byref(cfg), C.byref(rs),
                                            C.byref(o), C.c_void_p(ws.data_ptr()), ws.numel(), st), "nb_render_rays")
                 self.loss_buf.zero_()
@@ -198,9 +200,9 @@ class TrainStep:
                                             scale, C.c_void_p(self.loss_buf.data_ptr() + 4),
                                             C.c_void_p(self._d["rgb0"].data_ptr()), st))
             gk = {}
-            if phase != 2:
+            if phase in (None, 1, "fine"):
                 gk["d_rgb"] = self._d["rgb"]
-            if hier and phase != 1:
+            if hier and phase in (None, 2, "coarse"):
                 gk["d_rgb0"] = self._d["rgb0"]
             if gk:
                 gs = RenderGrads(*[_optptr(gk.get(k)) for k in ("d_rgb", "d_disp", "d_acc", "d_depth", "d_rgb0",
@@ -209,7 +211,7 @@ class TrainStep:
                                                     C.byref(rs), C.byref(gs), C.c_void_p(ws.data_ptr()), ws.numel(),
                                                     C.c_void_p(self.gc.data_ptr()), _optptr(self.gf), st),
                       "nb_render_rays_backward")
-            if in_kernel and phase != 1:
+            if in_kernel and phase in (None, 2):
                 check(lib().nb_rng_advance(C.c_void_p(self.rng_state.data_ptr()), st), "nb_rng_advance")
         return self.loss_buf
 
@@ -236,6 +238,31 @@ class TrainStep:
         """Everything of one iteration that runs on the GPU, in stream order (capturable in a CUDA graph)."""
         loss = self.forward_backward(rays, target, rnd, force_pack=True, zero_bucket=False)
         self.allreduce()
+        self._fused_adam()
+        return loss
+
+    def _device_iteration_two_streams(self, rays, target):
+        """Single-GPU iteration with the two networks' backward passes on two streams (they share nothing: own d_raw,
+        records, partial sums and gradient buffers).  Every heavy kernel is a persistent one-CTA-per-SM launch over a
+        static split of its tiles, so a kernel's SMs fall idle one by one at its end; with a second, independent chain
+        in the graph the block scheduler fills those tails (and the gaps of the small kernels) with the other chain's
+        CTAs.  NB_BWD_STREAMS=0 keeps the single chain."""
+        main = torch.cuda.current_stream(self.dev)
+        if self._side is None:
+            self._side = torch.cuda.Stream(self.dev)
+        loss = self.forward_backward(rays, target, force_pack=True, zero_bucket=False, phase="fwd")
+        fork = torch.cuda.Event()
+        fork.record(main)
+        self._side.wait_event(fork)
+        with torch.cuda.stream(self._side):
+            self.forward_backward(rays, target, force_pack=False, zero_bucket=False, phase="coarse")
+            join = torch.cuda.Event()
+            join.record(self._side)
+        self.forward_backward(rays, target, force_pack=False, zero_bucket=False, phase="fine")
+        main.wait_event(join)
+        if self.device_rng and (bool(self.perturb) or (self.noise or 0.0) > 0.0):
+            with torch.cuda.device(self.dev):
+                check(lib().nb_rng_advance(C.c_void_p(self.rng_state.data_ptr()), _stream()), "nb_rng_advance")
         self._fused_adam()
         return loss
 
@@ -302,7 +329,9 @@ class TrainStep:
             try:
                 graph = torch.cuda.CUDAGraph()
                 with torch.cuda.graph(graph):
-                    if self.world == 1 or self.mf is None or not self._overlap:
+                    if self.world == 1 and self.mf is not None and self.I > 0 and self._bwd_streams:
+                        self._device_iteration_two_streams(s_rays, s_tgt)
+                    elif self.world == 1 or self.mf is None or not self._overlap:
                         self._device_iteration(s_rays, s_tgt)
                     else:
                         self._device_iteration_overlapped(s_rays, s_tgt)
