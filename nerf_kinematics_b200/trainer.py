@@ -88,9 +88,12 @@ class TrainStep:
         self._bwd_streams = bool(int(os.environ.get("NB_BWD_STREAMS", "1")))
         self._side = None
         self._overlap = bool(int(os.environ.get("NB_OVERLAP_ALLREDUCE", "1")))
+        # world > 1: 1 = forward + both backward chains as ONE graph, one all-reduce of the whole bucket, Adam;
+        # 0 = the three-graph form (fine all-reduce under the coarse backward)
+        self._dp_chains = bool(int(os.environ.get("NB_DP_CHAINS", "1"))) and self._bwd_streams
         # the backward kernels are persistent, one 215 KB CTA per SM: leave a few SMs to NCCL so that the fine network's
         # all-reduce really runs under the coarse network's backward (NB_BWD_SM_RESERVE, default 8 when world > 1)
-        if self.world > 1 and self.mf is not None and self._overlap:
+        if self.world > 1 and self.mf is not None and self._overlap and not self._dp_chains:
             lib().nb_set_option(b"bwd_sm_reserve", int(os.environ.get("NB_BWD_SM_RESERVE", "8")))
         self.launches_per_step = None  # kernels inside one captured iteration (graph mode)
         self.graph_replays = 0
@@ -163,8 +166,9 @@ class TrainStep:
 
     def forward_backward(self, rays, target, rnd=None, force_pack=False, zero_bucket=True, phase=None):
         """Render + loss + backward into the flat bucket.  Returns the (device) loss tensor [2] = (fine, coarse).
-        phase 1 / 2 split the call for the multi-GPU step: 1 = forward, losses and the fine network's backward,
-        2 = the coarse network's backward (so the fine gradients' all-reduce can run under it); None = everything."""
+        phase splits the call: 1 = forward, losses and the fine network's backward, 2 = the coarse network's backward
+        (three-graph data-parallel step: the fine gradients' all-reduce runs under it); "fwd" = forward and losses,
+        "fine" / "coarse" = one network's backward (the two-chain step); None = everything."""
         rays, target = _f32(rays, "rays"), _f32(target, "target")
         n, stride, dev = rays.shape[0], rays.shape[1], rays.device
         hc, _ = self.mc.prepare(self.prec, force=force_pack)
@@ -241,12 +245,15 @@ class TrainStep:
         self._fused_adam()
         return loss
 
-    def _device_iteration_two_streams(self, rays, target):
-        """Single-GPU iteration with the two networks' backward passes on two streams (they share nothing: own d_raw,
-        records, partial sums and gradient buffers).  Every heavy kernel is a persistent one-CTA-per-SM launch over a
-        static split of its tiles, so a kernel's SMs fall idle one by one at its end; with a second, independent chain
-        in the graph the block scheduler fills those tails (and the gaps of the small kernels) with the other chain's
-        CTAs.  NB_BWD_STREAMS=0 keeps the single chain."""
+    def _device_iteration_two_streams(self, rays, target, with_adam=True):
+        """Iteration with the two networks' backward passes as two parallel chains (after the losses they share nothing:
+        own d_raw, records, partial sums and gradient buffers).  Every heavy kernel is a persistent one-CTA-per-SM launch
+        over a static split of its tiles, so a kernel's SMs fall idle one by one at its end (a CTA has 10 or 11 tiles of
+        the fine pass, 3 or 4 of the coarse one); with a second, independent chain in the graph the block scheduler fills
+        those tails, and the gaps of the small kernels, with the other chain's CTAs.  Measured on one B200, same box:
+        1.52 -> 1.46 ms per step; forking earlier (coarse backward under the fine FORWARD, nb_render_rays_part) was
+        slower, 1.495 vs 1.470, and a stream priority for the fine chain changed nothing.  NB_BWD_STREAMS=0 keeps the
+        single chain.  with_adam=False: the data-parallel step, which all-reduces the bucket between this and Adam."""
         main = torch.cuda.current_stream(self.dev)
         if self._side is None:
             self._side = torch.cuda.Stream(self.dev)
@@ -263,7 +270,8 @@ class TrainStep:
         if self.device_rng and (bool(self.perturb) or (self.noise or 0.0) > 0.0):
             with torch.cuda.device(self.dev):
                 check(lib().nb_rng_advance(C.c_void_p(self.rng_state.data_ptr()), _stream()), "nb_rng_advance")
-        self._fused_adam()
+        if with_adam:
+            self._fused_adam()
         return loss
 
     def _device_iteration_overlapped(self, rays, target):
@@ -349,9 +357,13 @@ class TrainStep:
             ga, gb = torch.cuda.CUDAGraph(), torch.cuda.CUDAGraph()
             # (host-drawn random arrays cannot be shared between two calls: that configuration keeps one backward)
             host_rng = not self.device_rng and (bool(self.perturb) or (self.noise or 0.0) > 0.0)
-            gm = torch.cuda.CUDAGraph() if (self.mf is not None and self._overlap and not host_rng) else None
+            chains = self._dp_chains and self.mf is not None and self.I > 0 and not host_rng
+            gm = torch.cuda.CUDAGraph() if (self.mf is not None and self._overlap and not host_rng and not chains) else None
             with torch.cuda.graph(ga):
-                self.forward_backward(s_rays, s_tgt, force_pack=True, zero_bucket=False, phase=1 if gm is not None else None)
+                if chains:   # both backward chains in one graph, ONE all-reduce of the whole bucket after it
+                    self._device_iteration_two_streams(s_rays, s_tgt, with_adam=False)
+                else:
+                    self.forward_backward(s_rays, s_tgt, force_pack=True, zero_bucket=False, phase=1 if gm is not None else None)
             if gm is not None:
                 with torch.cuda.graph(gm):
                     self.forward_backward(s_rays, s_tgt, force_pack=False, zero_bucket=False, phase=2)

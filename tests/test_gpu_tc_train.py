@@ -300,7 +300,8 @@ def _train_setup(seed=0, **kw):
     mc, mf = nk.model_from_state_dict(sdc).to(DEV), nk.model_from_state_dict(sdf).to(DEV)
     g = load_golden("train_flexible")
     rays, tgt = g["rays"][:64].to(DEV), g["target"][:64].to(DEV)
-    st = TrainStep(mc, mf, N_samples=64, N_importance=128, perturb=0.0, white_bkgd=True, lrate=5e-3, lrate_decay=1, **kw)
+    kw.setdefault("perturb", 0.0)
+    st = TrainStep(mc, mf, N_samples=64, N_importance=128, white_bkgd=True, lrate=5e-3, lrate_decay=1, **kw)
     return st, mc, mf, rays, tgt
 
 
@@ -387,6 +388,24 @@ def test_cuda_graph_step_equals_eager_step():
         oa = render_chunk(rays, mca, mfa, N_samples=64, N_importance=128, white_bkgd=True, precision="bf16")
         ob = render_chunk(rays, mcb, mfb, N_samples=64, N_importance=128, white_bkgd=True, precision="bf16")
     assert maxdiff(oa["rgb"], ob["rgb"]) <= 1e-4
+
+
+def test_two_chain_graph_step_is_bit_identical_to_the_single_chain_step():
+    """The captured single-GPU iteration runs the coarse network's backward on a side stream, forked right after the coarse
+    loss (trainer._device_iteration_two_streams, nb_render_rays_part); the chains share no buffer, so losses and every
+    updated parameter must equal the single-chain graph's bit for bit -- with in-kernel jitter and noise on, too."""
+    res = []
+    for streams in (True, False):
+        st, mc, mf, rays, tgt = _train_setup(precision="bf16", cuda_graph=True, perturb=1.0, raw_noise_std=0.5, seed=3)
+        st._bwd_streams = streams
+        losses = [st.step(torch.roll(rays, i, 0), torch.roll(tgt, i, 0)).clone() for i in range(4)]
+        torch.cuda.synchronize()
+        res.append((losses, [p.detach().clone() for p in list(mc.parameters()) + list(mf.parameters())]))
+        st.close()
+    for la, lb in zip(res[0][0], res[1][0]):
+        assert torch.equal(la, lb)
+    for pa, pb in zip(res[0][1], res[1][1]):
+        assert torch.equal(pa, pb)
 
 
 def test_step_pixels_equals_step_on_gathered_rays():
