@@ -337,7 +337,10 @@ class TrainStep:
             try:
                 graph = torch.cuda.CUDAGraph()
                 with torch.cuda.graph(graph):
-                    if self.world == 1 and self.mf is not None and self.I > 0 and self._bwd_streams:
+                    # (random arrays drawn by torch cannot be shared between the forward and two backward calls: that
+                    # configuration keeps the single call)
+                    host_rng = not self.device_rng and (bool(self.perturb) or (self.noise or 0.0) > 0.0)
+                    if self.world == 1 and self.mf is not None and self.I > 0 and self._bwd_streams and not host_rng:
                         self._device_iteration_two_streams(s_rays, s_tgt)
                     elif self.world == 1 or self.mf is None or not self._overlap:
                         self._device_iteration(s_rays, s_tgt)
