@@ -199,6 +199,37 @@ enum : uint32_t { PF_WAIT_ACT = 4u, PF_WAIT_ENCD = 8u, PF_FIRST = 16u, PF_LAST =
 constexpr uint64_t kDescHiSw128 = ((uint64_t)1 << 16) | ((uint64_t)(1024 >> 4) << 32) | ((uint64_t)1 << 46) | ((uint64_t)2 << 61);
 constexpr uint64_t kDescHiSw64 = ((uint64_t)1 << 16) | ((uint64_t)(512 >> 4) << 32) | ((uint64_t)1 << 46) | ((uint64_t)4 << 61);
 
+// The MMA issuers' step program, built in shared memory at kernel start: one entry per ring slot.  x = byte offset of the A
+// operand half-block inside a tile's region, y = instruction descriptor, z = flags (PF_*; bits 0-1 = activation block to
+// wait for), w = X-record block the awaited operand is saved to (train launches).  Lane s of ONE warp builds stage s from
+// the plan's step0 / encd_wait (a single thread walking all ~90 entries sat on every launch's critical path before the
+// first __syncthreads: ~10 us of the fixed cost per launch measured by tools/fixed_cost_sweep.py).
+template <bool kTwoCta>
+__device__ __forceinline__ void build_step_program(const TcPlan& plan, uint4* prog, int s) {
+  if (s >= plan.n_stages) return;
+  const TcStage& st = plan.st[s];
+  int i = st.step0;
+  bool encd_pending = st.encd_wait != 0;  // the encoding block was rewritten by an earlier stage: its next reader waits for bar_encd
+  for (int kb = 0; kb < st.n_kb; ++kb) {
+    const int sidx = st.a_src[kb];
+    // SRC_BIAS: one K=16 MMA over channels 48..63 of the encoding block (channel 63 == 1) against a chunk that is
+    // zero except for the biases in element 63 -- only the second half-block of that chunk is ever loaded
+    for (int h = sidx == SRC_BIAS ? 1 : 0; h < 2; ++h) {
+      uint4 e;
+      e.x = (uint32_t)((sidx < 4 ? sidx : plan.n_act_blocks) * kBlockBytes + h * 64);
+      e.y = kTwoCta ? umma_idesc2(st.n_main) : umma_idesc(st.n_main);
+      e.z = sidx == SRC_BIAS ? PF_BIAS : 0u;
+      e.w = 0u;
+      if (h == 0 && sidx < 4) { e.z |= PF_WAIT_ACT | (uint32_t)sidx; e.w = (uint32_t)(plan.st[s - 1].rec_blk + sidx); }
+      if ((sidx == SRC_ENCD || sidx == SRC_BIAS) && encd_pending) { e.z |= PF_WAIT_ENCD; e.w = 1u; encd_pending = false; }
+      if (kb == 0 && h == 0) e.z |= PF_FIRST;
+      if (kb == st.n_kb - 1 && h == 1) e.z |= PF_LAST;
+      if ((kb | h) != 0) e.z |= PF_ACC;
+      prog[i++] = e;
+    }
+  }
+}
+
 // ------------------------------------------------------------------------------------ the kernel
 __global__ void __launch_bounds__(kThreadsTc, 1)
 mlp_tc_kernel(const __grid_constant__ TcPlan plan, const unsigned char* __restrict__ wpk, const float* __restrict__ bias_g,
@@ -244,34 +275,7 @@ mlp_tc_kernel(const __grid_constant__ TcPlan plan, const unsigned char* __restri
     }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
-  if (threadIdx.x == 96) {
-    // step program: x = byte offset of the A operand half-block inside a tile's region, y = instruction descriptor,
-    // z = flags (PF_*; bits 0-1 = activation block to wait for), w = X-record block the awaited operand is saved to
-    int i = 0;
-    bool encd_pending = false;  // the encoding block is being rewritten: its next reader waits for bar_encd
-    for (int s = 0; s < plan.n_stages; ++s) {
-      const TcStage& st = plan.st[s];
-      for (int kb = 0; kb < st.n_kb; ++kb) {
-        const int sidx = st.a_src[kb];
-        // SRC_BIAS: one K=16 MMA over channels 48..63 of the encoding block (channel 63 == 1) against a chunk that is
-        // zero except for the biases in element 63 -- only the second half-block of that chunk is ever loaded
-        for (int h = sidx == SRC_BIAS ? 1 : 0; h < 2; ++h) {
-          uint4 e;
-          e.x = (uint32_t)((sidx < 4 ? sidx : plan.n_act_blocks) * kBlockBytes + h * 64);
-          e.y = umma_idesc(st.n_main);
-          e.z = sidx == SRC_BIAS ? PF_BIAS : 0u;
-          e.w = 0u;
-          if (h == 0 && sidx < 4) { e.z |= PF_WAIT_ACT | (uint32_t)sidx; e.w = (uint32_t)(plan.st[s - 1].rec_blk + sidx); }
-          if ((sidx == SRC_ENCD || sidx == SRC_BIAS) && encd_pending) { e.z |= PF_WAIT_ENCD; e.w = 1u; encd_pending = false; }
-          if (kb == 0 && h == 0) e.z |= PF_FIRST;
-          if (kb == st.n_kb - 1 && h == 1) e.z |= PF_LAST;
-          if ((kb | h) != 0) e.z |= PF_ACC;
-          prog[i++] = e;
-        }
-      }
-      if (st.write_encd) encd_pending = true;
-    }
-  }
+  if (warp == 3) build_step_program<false>(plan, prog, lane);
   if (warp == 1) {  // TMEM: all 512 columns (one CTA per SM): tile t owns columns [256 t, 256 t + 256)
     asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "r"(512));
     asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
@@ -589,31 +593,7 @@ mlp_tc4_kernel(const __grid_constant__ TcPlan plan, const unsigned char* __restr
     }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
-  if (threadIdx.x == 32) {
-    // step program (see mlp_tc_kernel): x = A operand offset inside a tile's region, y = instruction descriptor, z = flags
-    int i = 0;
-    bool encd_pending = false;
-    for (int s = 0; s < plan.n_stages; ++s) {
-      const TcStage& st = plan.st[s];
-      for (int kb = 0; kb < st.n_kb; ++kb) {
-        const int sidx = st.a_src[kb];
-        for (int h = sidx == SRC_BIAS ? 1 : 0; h < 2; ++h) {
-          uint4 e;
-          e.x = (uint32_t)((sidx < 4 ? sidx : plan.n_act_blocks) * kBlockBytes + h * 64);
-          e.y = umma_idesc(st.n_main);
-          e.z = sidx == SRC_BIAS ? PF_BIAS : 0u;
-          e.w = 0u;
-          if (h == 0 && sidx < 4) e.z |= PF_WAIT_ACT | (uint32_t)sidx;
-          if ((sidx == SRC_ENCD || sidx == SRC_BIAS) && encd_pending) { e.z |= PF_WAIT_ENCD; encd_pending = false; }
-          if (kb == 0 && h == 0) e.z |= PF_FIRST;
-          if (kb == st.n_kb - 1 && h == 1) e.z |= PF_LAST;
-          if ((kb | h) != 0) e.z |= PF_ACC;
-          prog[i++] = e;
-        }
-      }
-      if (st.write_encd) encd_pending = true;
-    }
-  }
+  if (warp == 1) build_step_program<false>(plan, prog, lane);
   if (warp == 1) {  // TMEM: all 512 columns; tile slot t owns columns [128 t, 128 t + 128)
     asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "r"(512));
     asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
@@ -878,30 +858,7 @@ mlp_tc2_kernel(const __grid_constant__ TcPlan plan, const unsigned char* __restr
     }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
-  if (threadIdx.x == 96) {
-    int i = 0;
-    bool encd_pending = false;
-    for (int s = 0; s < plan.n_stages; ++s) {
-      const TcStage& st = plan.st[s];
-      for (int kb = 0; kb < st.n_kb; ++kb) {
-        const int sidx = st.a_src[kb];
-        for (int h = sidx == SRC_BIAS ? 1 : 0; h < 2; ++h) {
-          uint4 e;
-          e.x = (uint32_t)((sidx < 4 ? sidx : plan.n_act_blocks) * kBlockBytes + h * 64);
-          e.y = umma_idesc2(st.n_main);
-          e.z = sidx == SRC_BIAS ? PF_BIAS : 0u;
-          e.w = 0u;
-          if (h == 0 && sidx < 4) e.z |= PF_WAIT_ACT | (uint32_t)sidx;
-          if ((sidx == SRC_ENCD || sidx == SRC_BIAS) && encd_pending) { e.z |= PF_WAIT_ENCD; encd_pending = false; }
-          if (kb == 0 && h == 0) e.z |= PF_FIRST;
-          if (kb == st.n_kb - 1 && h == 1) e.z |= PF_LAST;
-          if ((kb | h) != 0) e.z |= PF_ACC;
-          prog[i++] = e;
-        }
-      }
-      if (st.write_encd) encd_pending = true;
-    }
-  }
+  if (warp == 3) build_step_program<true>(plan, prog, lane);
   if (warp == 1) {  // TMEM: all 512 columns in both CTAs of the pair; stream t owns columns [256 t, 256 t + 256)
     asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "r"(512));
     asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;");
@@ -1264,9 +1221,21 @@ static bool build_plan(const Graph& g, TcPlan& plan, std::vector<PackSeg>& segs,
   for (int s = 0; s < plan.n_stages; ++s)
     if (plan.st[s].n_kb > kMaxKB) { *why = "too many K blocks"; return false; }
   plan.n_bias = boff;
+  // entry counts of the step program; each stage's first entry and its "wait for the direction encoding" flag, so that the
+  // kernels can build the program one stage per lane
   plan.n_steps = 0;
-  for (int s = 0; s < plan.n_stages; ++s)
-    for (int kb = 0; kb < plan.st[s].n_kb; ++kb) plan.n_steps += plan.st[s].a_src[kb] == SRC_BIAS ? 1 : 2;
+  bool encd_pending = false;
+  for (int s = 0; s < plan.n_stages; ++s) {
+    TcStage& st = plan.st[s];
+    st.step0 = plan.n_steps;
+    st.encd_wait = 0;
+    for (int kb = 0; kb < st.n_kb; ++kb) {
+      const int sidx = st.a_src[kb];
+      if ((sidx == SRC_ENCD || sidx == SRC_BIAS) && encd_pending) { st.encd_wait = 1; encd_pending = false; }
+      plan.n_steps += sidx == SRC_BIAS ? 1 : 2;
+    }
+    if (st.write_encd) encd_pending = true;
+  }
   w_bytes = woff;
   return true;
 }

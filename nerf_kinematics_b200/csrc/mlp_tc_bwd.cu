@@ -108,26 +108,25 @@ mlp_tc_dgrad_kernel(const __grid_constant__ BwPlan plan, const BwArgs a) {
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const long long n_tiles = (a.n_points + kTileM - 1) / kTileM;
 
-  if (threadIdx.x == 192) {
-    // MMA issuer step program, one entry per K-block: x = byte offset of the A operand block from the gradient
-    // tiles' base (the d_raw tile follows them), y = instruction descriptor, z = flags, w = dZ-record block the
+  if (warp == 6 && lane < plan.n_stages) {
+    // MMA issuer step program, one entry per K-block (lane s builds stage s): x = byte offset of the A operand block from
+    // the gradient tiles' base (the d_raw tile follows them), y = instruction descriptor, z = flags, w = dZ-record block the
     // awaited gradient block is saved to
-    int i = 0;
-    for (int s = 0; s < plan.n_stages; ++s) {
-      const BwStage& st = plan.st[s];
-      for (int kb = 0; kb < st.n_kb; ++kb) {
-        const int sidx = st.a_src[kb];
-        uint4 e;
-        e.x = (uint32_t)((sidx < 4 ? sidx : a.n_g_blocks) * kBlockBytes);
-        e.y = umma_idesc(st.n_main);
-        e.z = (s & 1) ? BF_BUF1 : 0u;
-        e.w = 0u;
-        if (sidx < 4) { e.z |= BF_WAIT_ACT | (uint32_t)sidx; e.w = (uint32_t)(plan.st[s - 1].drec_blk + sidx); }
-        if (st.k_steps[kb] == 1) e.z |= BF_K1;
-        if (kb != 0) e.z |= BF_ACC;
-        if (kb == st.n_kb - 1) e.z |= BF_LAST;
-        prog[i++] = e;
-      }
+    const int s = lane;
+    const BwStage& st = plan.st[s];
+    int i = st.step0;
+    for (int kb = 0; kb < st.n_kb; ++kb) {
+      const int sidx = st.a_src[kb];
+      uint4 e;
+      e.x = (uint32_t)((sidx < 4 ? sidx : a.n_g_blocks) * kBlockBytes);
+      e.y = umma_idesc(st.n_main);
+      e.z = (s & 1) ? BF_BUF1 : 0u;
+      e.w = 0u;
+      if (sidx < 4) { e.z |= BF_WAIT_ACT | (uint32_t)sidx; e.w = (uint32_t)(plan.st[s - 1].drec_blk + sidx); }
+      if (st.k_steps[kb] == 1) e.z |= BF_K1;
+      if (kb != 0) e.z |= BF_ACC;
+      if (kb == st.n_kb - 1) e.z |= BF_LAST;
+      prog[i++] = e;
     }
   }
   if (threadIdx.x == 0) {
@@ -668,7 +667,10 @@ bool bw_build_plan(const Graph& g, PackedBf16* p, std::vector<PackSegT>& segs, c
     if (bw.st[s].n_kb > kMaxKB) { *why = "too many K blocks"; return false; }
   bw.ring_stage_bytes = (int)round_up(ring_max, 1024);
   bw.n_steps = 0;
-  for (int s = 0; s < bw.n_stages; ++s) bw.n_steps += bw.st[s].n_kb;
+  for (int s = 0; s < bw.n_stages; ++s) {
+    bw.st[s].step0 = bw.n_steps;
+    bw.n_steps += bw.st[s].n_kb;
+  }
   bw.draw_blk = bw.drec_blocks++;
   p->wt_bytes = woff;
 

@@ -54,6 +54,8 @@ struct TcStage {
   int write_encd;     // 1: the position-encoding block is dead after this stage's MMAs; its epilogue re-fills it
                       //    with the direction encoding
   int rec_blk;        // train: first block of this stage's activations in the per-tile record (X record)
+  int step0;          // index of the stage's first entry in the MMA issuers' step program
+  int encd_wait;      // 1: the stage's first reader of the direction-encoding block waits for its re-fill
 };
 
 struct TcPlan {
@@ -75,6 +77,7 @@ struct BwStage {
   int mask_blk;         // first X-record block of the ReLU mask, -1 = none (linear layer input)
   int n_out;            // n_main / 64 gradient blocks written
   int drec_blk;         // first block of this stage's output in the per-tile dZ record
+  int step0;            // index of the stage's first entry in the MMA issuer's step program
 };
 struct BwPlan {
   int n_stages, drec_blocks, ring_stage_bytes;
