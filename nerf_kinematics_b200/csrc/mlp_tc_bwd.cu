@@ -514,26 +514,39 @@ mlp_tc_wgrad_kernel(const __grid_constant__ WgPlan plan, const __grid_constant__
   }
 }
 
-// grad[w] += (sum over the unit's CTAs of the partial) / scale ; same for the bias.  Deterministic order.
+// grad[w] += (sum over the unit's CTAs of the partial) / scale ; same for the bias.  Deterministic order (partial p0 first).
+// Four consecutive accumulator elements per thread (16-byte loads of the partials: same row, same X block).
 __global__ void wgrad_reduce_kernel(const __grid_constant__ WgPlan plan, const __grid_constant__ WgArgs a,
                                     const unsigned* __restrict__ absmax_bits, float* __restrict__ grad) {
   const WgUnit& u = plan.u[blockIdx.y];
   const int Ntot = 64 * u.n_x, M = 64 * u.m_blocks;
-  const int e = blockIdx.x * blockDim.x + threadIdx.x;
+  const int t = blockIdx.x * blockDim.x + threadIdx.x;
+  const int n4 = M * Ntot / 4;
   const int p0 = a.part0[blockIdx.y], p1 = a.part0[blockIdx.y + 1];
   const float inv = 1.0f / grad_scale_from(*absmax_bits);
-  if (e < M * Ntot) {
+  if (t < n4) {
+    const int e = 4 * t;
     const int row = e / Ntot, c = e - row * Ntot;
     const int xs = c >> 6, cc = c & 63;
     const int wr = row - u.row0;
     if (wr < 0 || wr >= u.out_rows || cc >= u.x_valid[xs]) return;
-    float s = 0.0f;
-    for (int p = p0; p < p1; ++p) s += a.part_w[(size_t)p * kPartFloats + e];
+    float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
+    const float4* src = reinterpret_cast<const float4*>(a.part_w) + t;
+#pragma unroll 4
+    for (int p = p0; p < p1; ++p) {
+      const float4 v = src[(size_t)p * (kPartFloats / 4)];
+      s.x += v.x; s.y += v.y; s.z += v.z; s.w += v.w;
+    }
     // X-record blocks 0 / 1 are the encodings (true values); every other block holds kActScale * activation
     const float xinv = u.x_blk[xs] >= 2 ? kInvActScale : 1.0f;
-    grad[u.w_off + (long long)wr * u.ld + u.x_col0[xs] + cc] += s * inv * xinv;
-  } else if (e < M * Ntot + 256) {
-    const int j = e - M * Ntot, wr = j - u.row0;
+    float* g = grad + u.w_off + (long long)wr * u.ld + u.x_col0[xs] + cc;
+    const int nv = u.x_valid[xs] - cc;   // >= 1
+    g[0] += s.x * inv * xinv;
+    if (nv > 1) g[1] += s.y * inv * xinv;
+    if (nv > 2) g[2] += s.z * inv * xinv;
+    if (nv > 3) g[3] += s.w * inv * xinv;
+  } else if (t < n4 + 256) {
+    const int j = t - n4, wr = j - u.row0;
     if (u.b_off < 0 || wr < 0 || wr >= u.out_rows) return;
     float s = 0.0f;
     for (int p = 4 * p0; p < 4 * p1; ++p) s += a.part_b[(size_t)p * 256 + j];
@@ -887,7 +900,7 @@ int tc_backward(const nb_model* m, int64_t n_points, float* d_raw, void* ws, siz
   const int wgrid = wa.part0[p->wg.n_units];
   mlp_tc_wgrad_kernel<<<wgrid, kThreadsWg, wg_smem_bytes(), stream>>>(p->wg, wa);
   NB_LAUNCHED();
-  dim3 rgrid((unsigned)ceil_div(kPartFloats + 256, 256), (unsigned)p->wg.n_units);
+  dim3 rgrid((unsigned)ceil_div(kPartFloats / 4 + 256, 256), (unsigned)p->wg.n_units);
   wgrad_reduce_kernel<<<rgrid, 256, 0, stream>>>(p->wg, wa, absmax, grad);
   NB_LAUNCHED();
   return NB_OK;
