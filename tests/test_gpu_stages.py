@@ -245,6 +245,23 @@ def test_sample_fine_two_ray_kernel_equals_one_ray_kernel():
         assert maxdiff(sd1, sd0) <= 2e-6                        # a different summation order
         ref, _ = torch.sort(torch.cat((z, zs1), -1), -1)
         assert torch.equal(zf1, ref)
+        # random u (the train step): the two-ray kernel sorts the uniforms first, the one-ray kernel sorts the samples
+        u = torch.rand(n, ns, generator=gen)
+        u[5] = 0.0
+        u[6, ::2] = u[6, 1::2]                                  # repeated uniforms
+        u = u.to(DEV)
+        rnd = {}
+        for v in (0, 1):
+            old = lib().nb_set_option(b"sample_fine2", v)
+            try:
+                rnd[v] = ops.sample_fine(z, w, ns, u=u, want_std=True)
+            finally:
+                lib().nb_set_option(b"sample_fine2", old)
+        assert torch.equal(rnd[1][0], rnd[0][0])
+        assert maxdiff(rnd[1][2], rnd[0][2]) <= 2e-6
+        _, zs_u, _ = ops.sample_fine(z, w, ns, u=u, want_samples=True)   # (one-ray kernel: samples in the caller's order)
+        ref, _ = torch.sort(torch.cat((z, zs_u), -1), -1)
+        assert torch.equal(rnd[1][0], ref)
 
 
 def test_mse_loss():
