@@ -528,7 +528,11 @@ def run_train(args):
             "vs_baseline": None, "dtype": "f16" if prec_name != "fp32" else "f32", "data": "synthetic",
             "config": shared_config("train", args, world),
             "impl_detail": {"mlp_precision": "fp16 operands (tcgen05 kind::f16), fp32 accumulation" if prec_name != "fp32" else "fp32",
-                            "cuda_graph": bool(step.use_graph), "timed_region": "median of %d back-to-back repeats of exactly "
+                            "cuda_graph": bool(step.use_graph),
+                            "graph_shape": ("forward, then the two networks' backward passes as parallel branches, Adam"
+                                            if getattr(step, "_bwd_streams", False) else "one chain")
+                            + ("; one all-reduce of the whole gradient bucket before Adam" if world > 1 else ""),
+                            "timed_region": "median of %d back-to-back repeats of exactly "
                             "K steps" % R, "repeat_ms_per_step": [1e3 * t / K for t in ts_res]},
             "e2e": {"value": e2e, "unit": "rays/s", "h2d_bytes_per_step": n_rand * 9 * 4 * world,
                     "d2h_bytes_per_step": 8 * world, "ms_per_step": 1e3 * t_e2e / K},
