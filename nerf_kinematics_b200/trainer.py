@@ -11,9 +11,11 @@ Two B200-side additions over the reference loop, both optional:
   * fused Adam (nb_adam_step): one launch per network instead of torch's ~7 multi-tensor launches; the moments live
     in flat buffers that a regular torch.optim.Adam object aliases, so `optimizer.state_dict()` keeps the reference's
     checkpoint layout (train_nerf.py:401-414);
-  * CUDA graph: the whole device side of an iteration (weight repack, render, loss, backward, all-reduce, Adam) is
-    captured once per batch shape and replayed with one launch; learning rate and bias corrections are read from a
-    small device array refreshed before each replay.
+  * CUDA graph: the whole device side of an iteration (weight repack, render, loss, backward, Adam) is captured once
+    per batch shape and replayed with one launch; learning rate and bias corrections are read from a small device
+    array refreshed before each replay.  Inside the graph the two networks' backward passes are parallel branches
+    (_device_iteration_two_streams); with more than one rank the graph ends before Adam, the whole bucket is
+    all-reduced once, and a second graph holds Adam.
 """
 import ctypes as C
 import os
@@ -251,7 +253,7 @@ class TrainStep:
         over a static split of its tiles, so a kernel's SMs fall idle one by one at its end (a CTA has 10 or 11 tiles of
         the fine pass, 3 or 4 of the coarse one); with a second, independent chain in the graph the block scheduler fills
         those tails, and the gaps of the small kernels, with the other chain's CTAs.  Measured on one B200, same box:
-        1.52 -> 1.46 ms per step; forking earlier (coarse backward under the fine FORWARD, nb_render_rays_part) was
+        1.52 -> 1.46 ms per step; forking earlier (coarse backward under the fine FORWARD, the chunk renderer split in two calls) was
         slower, 1.495 vs 1.470, and a stream priority for the fine chain changed nothing.  NB_BWD_STREAMS=0 keeps the
         single chain.  with_adam=False: the data-parallel step, which all-reduces the bucket between this and Adam."""
         main = torch.cuda.current_stream(self.dev)
